@@ -1,0 +1,168 @@
+/*
+ * pa_b200.h - C ABI of libpa_b200.so: B200 (sm_100a) paged-attention hot path.
+ *
+ * This is the drop-in boundary for ONE path of HeduAiDev/vllm-from-scratch:
+ * paged-attention decode over a block table, the KV-cache slot write
+ * (reshape-and-cache) and block copy / swap.  The reference has no FFI of its
+ * own (it is pure Python); the entry points below are what a binding for the
+ * module-level functions of 01_paged_attention/paged_attention.py would bind.
+ * Each entry cites the reference interface it replaces (paths relative to the
+ * reference root).  INTEGRATION.md shows the reference-side stub.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; no torch / C++ types cross this boundary;
+ *  - every pointer is a DEVICE pointer unless the name says "host";
+ *  - all launches are asynchronous on the caller's `stream`; nothing here
+ *    synchronises, allocates device memory or keeps caller pointers;
+ *  - return value: 0 (PA_OK) or a negative PaStatus; never throws;
+ *  - strides are in ELEMENTS of the cache dtype; the head_dim axis is
+ *    contiguous everywhere;
+ *  - thread-safety: stateless launchers (one internal mutex guards a small
+ *    tensor-map cache); one process per GPU in multi-GPU use.
+ */
+#ifndef PA_B200_H_
+#define PA_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PA_B200_ABI_VERSION 1
+
+typedef enum PaStatus {
+  PA_OK = 0,
+  PA_ERR_BAD_ARG = -1,      /* null pointer, negative size, g not integral ...   */
+  PA_ERR_UNSUPPORTED = -2,  /* shape / dtype outside the supported set           */
+  PA_ERR_MISALIGNED = -3,   /* pointer or stride alignment requirement not met   */
+  PA_ERR_WORKSPACE = -4,    /* workspace too small                                */
+  PA_ERR_CUDA = -5,         /* a CUDA runtime / driver call failed                */
+  PA_ERR_NO_DEVICE = -6     /* no sm_100 device is current                        */
+} PaStatus;
+
+typedef enum PaDtype { PA_BF16 = 0, PA_F32 = 1 } PaDtype;
+
+/* A paged KV cache for ONE layer, described by strides so that both reference
+ * layouts are accepted without a transposing copy:
+ *   'hbsd'  kv_cache[2, NB, Hkv, BS, D]   (01_paged_attention/paged_attention.py:26-30, :69)
+ *           k = kv_cache[0], v = kv_cache[1]; stride_block = Hkv*BS*D, stride_head = BS*D, stride_slot = D
+ *   'bshd'  k_cache / v_cache [NB, BS, H, D]   (05_mini_vllm/mini_vllm.py:544-552)
+ *           stride_block = BS*H*D, stride_slot = H*D, stride_head = D                          */
+typedef struct PaKvCache {
+  void* k;                /* K plane base (block 0, head 0, slot 0)               */
+  void* v;                /* V plane base                                          */
+  int64_t stride_block;
+  int64_t stride_head;
+  int64_t stride_slot;
+  int32_t num_blocks;     /* NB                                                    */
+  int32_t num_kv_heads;   /* Hkv                                                   */
+  int32_t block_size;     /* BS, tokens per block                                  */
+  int32_t head_dim;       /* D                                                     */
+  int32_t dtype;          /* PaDtype of the cache AND of q / out / key / value     */
+  int32_t reserved;
+} PaKvCache;
+
+/* ---- introspection ------------------------------------------------------ */
+int pa_abi_version(void);
+const char* pa_status_string(int status);
+/* Number of persistent decode workers (warps) the current device runs; the
+ * split-K plan and the workspace size depend on it.  <0 on error.           */
+int pa_decode_num_workers(void);
+
+/* ---- decode (replaces paged_attention_decode, paged_attention.py:67-101,
+ *      batched: semantics = that function looped over the batch) -----------
+ * q   [batch, num_q_heads, D]   (q_stride_b / q_stride_h in elements)
+ * out [batch, num_q_heads, D]   same dtype as q
+ * block_tables int32 [batch, bt_stride]; entries beyond ceil(seq_len/BS) are
+ *   never dereferenced.  seq_lens int32 [batch]; seq_len == 0 -> zeros.
+ * softmax scale is 1/sqrt(D) (paged_attention.py:80).
+ * Two launches: the split-K ("flash-decoding") kernel over (sequence, KV head,
+ * context partition) work ranges and a small cross-partition reduce kernel.
+ * workspace: pa_decode_workspace_bytes() bytes, 16-byte aligned, contents
+ *   undefined on entry, owned by the caller.                                 */
+size_t pa_decode_workspace_bytes(int32_t batch, int32_t num_q_heads,
+                                 int32_t num_kv_heads, int32_t head_dim);
+
+int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h,
+              void* out, int64_t o_stride_b, int64_t o_stride_h,
+              const PaKvCache* cache,
+              const int32_t* block_tables, int32_t bt_stride,
+              const int32_t* seq_lens,
+              int32_t batch, int32_t num_q_heads,
+              void* workspace, size_t workspace_bytes,
+              void* stream /* cudaStream_t */);
+
+/* ---- slot mapping on the device (replaces compute_slot_mapping,
+ *      paged_attention.py:54-64, and Scheduler._compute_slot_mapping,
+ *      mini_vllm.py:209-219): for i in [0, num_tokens)
+ *        pos = start_pos + i;  slots[i] = block_table[pos / BS] * BS + pos % BS
+ * block_table int32 (device), slots int64 (device).  Integer-exact.          */
+int pa_slot_mapping(const int32_t* block_table, int32_t start_pos, int32_t num_tokens,
+                    int32_t block_size, int64_t* slots, void* stream);
+
+/* ---- KV slot write (replaces the write loops paged_attention.py:48-51 and
+ *      :119-123, and the scatter mini_vllm.py:424-427) ----------------------
+ * key/value [num_tokens, Hkv, D] with token / head strides in elements.
+ * slot_mapping int64 [num_tokens]: slot = block*BS + offset; slot < 0 skips
+ * the token (padding).  Pure byte copy: bit-exact.                           */
+int pa_reshape_and_cache(const void* key, const void* value,
+                         int64_t kv_stride_token, int64_t kv_stride_head,
+                         const PaKvCache* cache,
+                         const int64_t* slot_mapping, int32_t num_tokens,
+                         void* stream);
+
+/* ---- block copy (no reference code; definitional:
+ *      plane[p][dst] = plane[p][src] for every plane and pair;
+ *      prose: BLOG_PART1_V2.md:748-777) --------------------------------------
+ * A pool is `num_planes` planes (2 x layers for [2, L, NB, ...]) of blocks;
+ * `pairs` int64 [num_pairs, 2] = (src, dst) on the DEVICE.  The dst set must
+ * be disjoint from the src set.  block_bytes must be a multiple of 16.       */
+int pa_copy_blocks(void* base, int64_t plane_stride_bytes, int32_t num_planes,
+                   int64_t block_stride_bytes, int64_t block_bytes,
+                   const int64_t* pairs, int32_t num_pairs, void* stream);
+
+/* ---- swap (no reference code; same definition between a device pool and a
+ *      pinned-host pool of identical per-block layout) -----------------------
+ * `pairs_host` int64 [num_pairs, 2] = (src_block, dst_block) in HOST memory
+ * (it is walked on the host to issue the copies).  direction: 0 = device ->
+ * host (swap-out), 1 = host -> device (swap-in).  Copies are issued as
+ * cudaMemcpy2DAsync (all planes of a run of consecutive blocks per call) on
+ * `stream`, which should be a side stream; the caller records an event.      */
+int pa_swap_blocks(void* dst_base, int64_t dst_plane_stride_bytes, int64_t dst_block_stride_bytes,
+                   const void* src_base, int64_t src_plane_stride_bytes, int64_t src_block_stride_bytes,
+                   int32_t num_planes, int64_t block_bytes,
+                   const int64_t* pairs_host, int32_t num_pairs, int32_t direction,
+                   void* stream);
+
+/* ---- prefill attention (replaces the attention half of
+ *      paged_attention_prefill, paged_attention.py:125-136, extended with
+ *      history: query chunk at positions [start_pos, start_pos + num_tokens)
+ *      attends causally to positions [0, start_pos + i] read THROUGH the block
+ *      table - the KV of the chunk must already be in the cache, i.e. call
+ *      pa_reshape_and_cache first) ------------------------------------------------
+ * q / out [num_tokens, num_q_heads, D].  One sequence per call.
+ * Round-1 implementation: every query token is a decode "sequence" of length
+ * start_pos + i + 1 over the shared block table (same kernels, same numerics
+ * as pa_decode); a dedicated tcgen05 prefill kernel is the next row of the
+ * scope table.                                                               */
+size_t pa_prefill_workspace_bytes(int32_t num_tokens, int32_t num_q_heads,
+                                  int32_t num_kv_heads, int32_t head_dim);
+
+int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
+               void* out, int64_t o_stride_t, int64_t o_stride_h,
+               const PaKvCache* cache, const int32_t* block_table,
+               int32_t start_pos, int32_t num_tokens, int32_t num_q_heads,
+               void* workspace, size_t workspace_bytes,
+               void* stream);
+
+/* ---- test / tuning hook ---------------------------------------------------
+ * 0 = automatic kernel choice (default); 1 = force the generic CUDA-core
+ * decode kernel even for shapes the TMA kernel takes.  Returns the old value. */
+int pa_decode_force_path(int path);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PA_B200_H_ */

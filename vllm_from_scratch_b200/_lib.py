@@ -1,0 +1,81 @@
+"""ctypes binding of libpa_b200.so - the C ABI declared in include/pa_b200.h.
+
+There is NO fallback: if the library is missing or a call fails, a RuntimeError is raised.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import (POINTER, Structure, c_char_p, c_int, c_int32, c_int64, c_size_t, c_void_p)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpa_b200.so")
+
+PA_BF16 = 0
+PA_F32 = 1
+
+
+class PaKvCache(Structure):
+    """Mirror of `struct PaKvCache` (include/pa_b200.h)."""
+    _fields_ = [
+        ("k", c_void_p),
+        ("v", c_void_p),
+        ("stride_block", c_int64),
+        ("stride_head", c_int64),
+        ("stride_slot", c_int64),
+        ("num_blocks", c_int32),
+        ("num_kv_heads", c_int32),
+        ("block_size", c_int32),
+        ("head_dim", c_int32),
+        ("dtype", c_int32),
+        ("reserved", c_int32),
+    ]
+
+
+# name -> (restype, argtypes); one entry per symbol declared in include/pa_b200.h
+SIGNATURES = {
+    "pa_abi_version": (c_int, []),
+    "pa_status_string": (c_char_p, [c_int]),
+    "pa_decode_num_workers": (c_int, []),
+    "pa_decode_force_path": (c_int, [c_int]),
+    "pa_decode_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
+    "pa_decode": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
+                          c_void_p, c_int32, c_void_p, c_int32, c_int32, c_void_p, c_size_t, c_void_p]),
+    "pa_slot_mapping": (c_int, [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
+    "pa_reshape_and_cache": (c_int, [c_void_p, c_void_p, c_int64, c_int64, POINTER(PaKvCache), c_void_p,
+                                     c_int32, c_void_p]),
+    "pa_copy_blocks": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_int64, c_void_p, c_int32, c_void_p]),
+    "pa_swap_blocks": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int32, c_int64,
+                               c_void_p, c_int32, c_int32, c_void_p]),
+    "pa_prefill_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
+    "pa_prefill": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
+                           c_void_p, c_int32, c_int32, c_int32, c_void_p, c_size_t, c_void_p]),
+}
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    """Load the library once.  Fails loudly - the product path has no CPU fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -m vllm_from_scratch_b200.build` "
+            "(nvcc, sm_100a).  There is no CPU / PyTorch fallback for the paged-attention path.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)           # AttributeError if a declared symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    if lib.pa_abi_version() != 1:
+        raise RuntimeError(f"libpa_b200.so ABI version {lib.pa_abi_version()} != 1")
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().pa_status_string(rc).decode()
+        raise RuntimeError(f"{what} failed: {msg} (status {rc})")

@@ -1,0 +1,179 @@
+// C ABI of libpa_b200.so (include/pa_b200.h): argument validation, split-K planning
+// and kernel selection.  Nothing here touches torch; the Python host
+// (vllm_from_scratch_b200/paged_attention.py) passes raw device pointers and the
+// current stream.
+#include <atomic>
+#include <math.h>
+
+#include "../../include/pa_b200.h"
+#include "pa_common.cuh"
+
+namespace {
+
+std::atomic<int> g_force_path{0};
+
+int sm_count() {
+  static std::atomic<int> cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return -1; }
+  if (dev >= 0 && dev < 64 && cached[dev].load() > 0) return cached[dev].load();
+  int n = 0;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) { cudaGetLastError(); return -1; }
+  if (dev >= 0 && dev < 64) cached[dev].store(n);
+  return n;
+}
+
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct WsLayout {
+  size_t plan_off, ml_off, o_off, total;
+};
+
+// rows = partial rows per slot (tile_q), slots = segments + workers.
+WsLayout ws_layout(int batch, int64_t slots, int rows, int head_dim) {
+  WsLayout w;
+  w.plan_off = 0;
+  w.ml_off = align_up((size_t)(batch + 3) * 4, 256);
+  w.o_off = w.ml_off + align_up((size_t)slots * rows * sizeof(float2), 256);
+  w.total = w.o_off + align_up((size_t)slots * rows * head_dim * sizeof(float), 256);
+  return w;
+}
+
+__global__ void pa_iota_lens_kernel(int32_t* lens, int32_t first, int32_t n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) lens[i] = first + i;
+}
+
+}  // namespace
+
+extern "C" int pa_abi_version(void) { return PA_B200_ABI_VERSION; }
+
+extern "C" const char* pa_status_string(int status) {
+  switch (status) {
+    case PA_OK: return "ok";
+    case PA_ERR_BAD_ARG: return "bad argument";
+    case PA_ERR_UNSUPPORTED: return "unsupported shape or dtype";
+    case PA_ERR_MISALIGNED: return "misaligned pointer or stride";
+    case PA_ERR_WORKSPACE: return "workspace too small";
+    case PA_ERR_CUDA: return "CUDA call failed";
+    case PA_ERR_NO_DEVICE: return "no sm_100 device is current";
+    default: return "unknown status";
+  }
+}
+
+extern "C" int pa_decode_force_path(int path) { return g_force_path.exchange(path); }
+
+extern "C" int pa_decode_num_workers(void) {
+  const int sms = sm_count();
+  if (sms <= 0) return PA_ERR_NO_DEVICE;
+  return pa_decode_tma_workers(sms);
+}
+
+extern "C" size_t pa_decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
+                                            int32_t head_dim) {
+  if (batch <= 0 || num_q_heads <= 0 || num_kv_heads <= 0 || head_dim <= 0) return 256;
+  int sms = sm_count();
+  if (sms <= 0) sms = 148;                       // sizing without a device: assume a B200
+  const int g = (num_q_heads + num_kv_heads - 1) / num_kv_heads;
+  const int nt = (g + 7) / 8;
+  int ctas;
+  const int64_t slots_tma = (int64_t)batch * num_kv_heads + pa_decode_tma_workers(sms);
+  const int64_t slots_gen = (int64_t)batch * num_kv_heads * nt + pa_decode_generic_workers(sms, &ctas);
+  const size_t a = ws_layout(batch, slots_tma, 8 * nt, head_dim).total;
+  const size_t b = ws_layout(batch, slots_gen, 8, head_dim).total;
+  return a > b ? a : b;
+}
+
+extern "C" int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h, void* out, int64_t o_stride_b,
+                         int64_t o_stride_h, const PaKvCache* cache, const int32_t* block_tables,
+                         int32_t bt_stride, const int32_t* seq_lens, int32_t batch, int32_t num_q_heads,
+                         void* workspace, size_t workspace_bytes, void* stream) {
+  if (batch < 0 || !cache) return PA_ERR_BAD_ARG;
+  if (batch == 0) return PA_OK;
+  if (!q || !out || !cache->k || !cache->v || !block_tables || !seq_lens || !workspace) return PA_ERR_BAD_ARG;
+  if (cache->dtype != PA_BF16 && cache->dtype != PA_F32) return PA_ERR_UNSUPPORTED;
+  const int Hkv = cache->num_kv_heads, D = cache->head_dim, BS = cache->block_size;
+  if (Hkv <= 0 || D <= 0 || BS <= 0 || num_q_heads <= 0 || bt_stride < 0) return PA_ERR_BAD_ARG;
+  if (num_q_heads % Hkv != 0) return PA_ERR_BAD_ARG;
+  if (D > 256) return PA_ERR_UNSUPPORTED;
+  if (batch > PA_MAX_BATCH_SMEM) return PA_ERR_UNSUPPORTED;
+  if (reinterpret_cast<uintptr_t>(workspace) & 15) return PA_ERR_MISALIGNED;
+  const int sms = sm_count();
+  if (sms <= 0) return PA_ERR_NO_DEVICE;
+
+  PaDecodeParams p;
+  p.q = q; p.out = out; p.k = cache->k; p.v = cache->v;
+  p.block_tables = block_tables; p.seq_lens = seq_lens;
+  p.q_stride_b = q_stride_b; p.q_stride_h = q_stride_h;
+  p.o_stride_b = o_stride_b; p.o_stride_h = o_stride_h;
+  p.kv_stride_block = cache->stride_block; p.kv_stride_head = cache->stride_head; p.kv_stride_slot = cache->stride_slot;
+  p.bt_stride = bt_stride;
+  p.batch = batch; p.num_q_heads = num_q_heads; p.num_kv_heads = Hkv; p.head_dim = D; p.block_size = BS;
+  p.group = num_q_heads / Hkv;
+  p.pos_head = p.pos_block = 0;
+  p.scale_log2e = (float)((1.0 / sqrt((double)D)) * 1.4426950408889634);
+
+  const bool tma = g_force_path.load() != 1 && pa_decode_tma_supported(p, cache->dtype);
+  int ctas = 0;
+  if (tma) {
+    p.tile_q = 8 * ((p.group + 7) / 8);
+    p.q_tiles = 1;
+    p.num_workers = pa_decode_tma_workers(sms);
+  } else {
+    p.tile_q = 8;
+    p.q_tiles = (p.group + 7) / 8;
+    p.num_workers = pa_decode_generic_workers(sms, &ctas);
+  }
+  const int64_t slots = (int64_t)batch * Hkv * p.q_tiles + p.num_workers;
+  const WsLayout w = ws_layout(batch, slots, p.tile_q, D);
+  if (workspace_bytes < w.total) return PA_ERR_WORKSPACE;
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  p.plan = reinterpret_cast<int32_t*>(ws + w.plan_off);
+  p.part_ml = reinterpret_cast<float2*>(ws + w.ml_off);
+  p.part_o = reinterpret_cast<float*>(ws + w.o_off);
+
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = tma ? pa_launch_decode_tma(p, sms, st) : pa_launch_decode_generic(p, cache->dtype, ctas, st);
+  if (rc) return rc;
+  return pa_launch_reduce(p, cache->dtype, st);
+}
+
+// ---- prefill = one decode "sequence" per query token over the shared block table --------
+namespace {
+constexpr int kPrefillChunk = 4096;     // query tokens per decode launch (< PA_MAX_BATCH_SMEM)
+}
+
+extern "C" size_t pa_prefill_workspace_bytes(int32_t num_tokens, int32_t num_q_heads, int32_t num_kv_heads,
+                                             int32_t head_dim) {
+  const int chunk = num_tokens < kPrefillChunk ? (num_tokens > 0 ? num_tokens : 1) : kPrefillChunk;
+  return align_up((size_t)chunk * 4, 256) + pa_decode_workspace_bytes(chunk, num_q_heads, num_kv_heads, head_dim);
+}
+
+extern "C" int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t o_stride_t,
+                          int64_t o_stride_h, const PaKvCache* cache, const int32_t* block_table,
+                          int32_t start_pos, int32_t num_tokens, int32_t num_q_heads, void* workspace,
+                          size_t workspace_bytes, void* stream) {
+  if (num_tokens < 0 || start_pos < 0 || !cache) return PA_ERR_BAD_ARG;
+  if (num_tokens == 0) return PA_OK;
+  if (!workspace || (reinterpret_cast<uintptr_t>(workspace) & 15)) return PA_ERR_BAD_ARG;
+  if (cache->dtype != PA_BF16 && cache->dtype != PA_F32) return PA_ERR_UNSUPPORTED;
+  if (workspace_bytes < pa_prefill_workspace_bytes(num_tokens, num_q_heads, cache->num_kv_heads, cache->head_dim))
+    return PA_ERR_WORKSPACE;
+  const int es = cache->dtype == PA_F32 ? 4 : 2;
+  const int chunk_cap = num_tokens < kPrefillChunk ? num_tokens : kPrefillChunk;
+  const size_t lens_bytes = align_up((size_t)chunk_cap * 4, 256);
+  int32_t* lens = static_cast<int32_t*>(workspace);
+  uint8_t* dws = static_cast<uint8_t*>(workspace) + lens_bytes;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  for (int t0 = 0; t0 < num_tokens; t0 += kPrefillChunk) {
+    const int n = num_tokens - t0 < kPrefillChunk ? num_tokens - t0 : kPrefillChunk;
+    pa_iota_lens_kernel<<<(n + 255) / 256, 256, 0, st>>>(lens, start_pos + t0 + 1, n);
+    if (cudaGetLastError() != cudaSuccess) return PA_ERR_CUDA;
+    const int rc = pa_decode(static_cast<const uint8_t*>(q) + (int64_t)t0 * q_stride_t * es, q_stride_t, q_stride_h,
+                             static_cast<uint8_t*>(out) + (int64_t)t0 * o_stride_t * es, o_stride_t, o_stride_h,
+                             cache, block_table, /*bt_stride=*/0, lens, n, num_q_heads, dws,
+                             workspace_bytes - lens_bytes, stream);
+    if (rc) return rc;
+  }
+  return PA_OK;
+}

@@ -1,0 +1,222 @@
+// KV-cache data movement: slot write (reshape-and-cache), block copy, block swap.
+// All three are pure byte copies - bit-exact by construction - and HBM- (or PCIe-) bound.
+//
+//  * pa_reshape_and_cache : the slot-mapping scatter of new K/V rows.  Replaces the Python
+//    write loops 01_paged_attention/paged_attention.py:48-51 and :119-123 (layout
+//    [2, NB, Hkv, BS, D]) and the index_put 05_mini_vllm/mini_vllm.py:424-427 (layout
+//    [NB, BS, H, D]); the cache layout is described by strides, so one kernel serves both.
+//  * pa_copy_blocks / pa_swap_blocks : no reference code exists;
+//    definitional dst[b_dst] = src[b_src] over every plane of a pool.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/pa_b200.h"
+
+namespace {
+
+__device__ __forceinline__ uint4 ld_stream(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+struct RacParams {
+  const uint8_t* key;
+  const uint8_t* value;
+  uint8_t* k_cache;
+  uint8_t* v_cache;
+  const int64_t* slots;
+  int64_t src_stride_token, src_stride_head;           // bytes
+  int64_t stride_block, stride_head, stride_slot;      // bytes
+  int32_t num_tokens, num_heads, block_size;
+  int32_t row_units;                                   // units (16 B or esize) per [D] row
+  int64_t num_slots;                                   // NB * BS, for the bounds check
+};
+
+// One work item = one unit of one (token, head) row, for K and for V.  UNIT_T = uint4 when every
+// address is 16-byte aligned (the normal case), else the element type.  Each thread keeps UNROLL
+// independent loads in flight (2 * UNROLL with K and V).
+template <typename UNIT_T, int UNROLL>
+__global__ void __launch_bounds__(256)
+pa_reshape_and_cache_kernel(const RacParams p) {
+  const int64_t per_token = (int64_t)p.num_heads * p.row_units;
+  const int64_t total = (int64_t)p.num_tokens * per_token;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < total; base += stride * UNROLL) {
+    UNIT_T kv[UNROLL], vv[UNROLL];
+    int64_t dst[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const int64_t i = base + u * stride;
+      dst[u] = -1;
+      if (i < total) {
+        const int64_t t = i / per_token;
+        const int r = (int)(i - t * per_token);
+        const int h = r / p.row_units, c = r - h * p.row_units;
+        const int64_t slot = __ldg(p.slots + t);
+        if (slot >= 0 && slot < p.num_slots) {             // negative slot = padding token
+          const int64_t blk = slot / p.block_size, off = slot - blk * p.block_size;
+          const int64_t src = t * p.src_stride_token + h * p.src_stride_head + (int64_t)c * sizeof(UNIT_T);
+          dst[u] = blk * p.stride_block + h * p.stride_head + off * p.stride_slot + (int64_t)c * sizeof(UNIT_T);
+          kv[u] = *reinterpret_cast<const UNIT_T*>(p.key + src);
+          vv[u] = *reinterpret_cast<const UNIT_T*>(p.value + src);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      if (dst[u] >= 0) {
+        *reinterpret_cast<UNIT_T*>(p.k_cache + dst[u]) = kv[u];
+        *reinterpret_cast<UNIT_T*>(p.v_cache + dst[u]) = vv[u];
+      }
+    }
+  }
+}
+
+// grid.x = chunks per block, grid.y = pair, grid.z = plane.  One CTA copies kCopyChunk bytes.
+constexpr int kCopyThreads = 256;
+constexpr int kCopyUnroll = 4;
+constexpr int kCopyChunk = kCopyThreads * kCopyUnroll * 16;      // 16 KiB
+
+__global__ void __launch_bounds__(kCopyThreads)
+pa_copy_blocks_kernel(uint8_t* base, int64_t plane_stride, int64_t block_stride, int64_t block_bytes,
+                      const int64_t* __restrict__ pairs) {
+  const int64_t src_b = __ldg(pairs + 2 * blockIdx.y), dst_b = __ldg(pairs + 2 * blockIdx.y + 1);
+  if (src_b == dst_b) return;
+  const uint8_t* src = base + blockIdx.z * plane_stride + src_b * block_stride;
+  uint8_t* dst = base + blockIdx.z * plane_stride + dst_b * block_stride;
+  const int64_t lo = (int64_t)blockIdx.x * kCopyChunk;
+  uint4 v[kCopyUnroll];
+#pragma unroll
+  for (int u = 0; u < kCopyUnroll; ++u) {
+    const int64_t o = lo + ((int64_t)u * kCopyThreads + threadIdx.x) * 16;
+    if (o < block_bytes) v[u] = ld_stream(reinterpret_cast<const uint4*>(src + o));
+  }
+#pragma unroll
+  for (int u = 0; u < kCopyUnroll; ++u) {
+    const int64_t o = lo + ((int64_t)u * kCopyThreads + threadIdx.x) * 16;
+    if (o < block_bytes) *reinterpret_cast<uint4*>(dst + o) = v[u];
+  }
+}
+
+__global__ void pa_slot_mapping_kernel(const int32_t* __restrict__ bt, int32_t start_pos, int32_t n, int32_t bs,
+                                       int64_t* __restrict__ slots) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int pos = start_pos + i;
+  slots[i] = (int64_t)__ldg(bt + pos / bs) * bs + pos % bs;
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+}  // namespace
+
+extern "C" int pa_slot_mapping(const int32_t* block_table, int32_t start_pos, int32_t num_tokens,
+                               int32_t block_size, int64_t* slots, void* stream) {
+  if (num_tokens < 0 || start_pos < 0 || block_size <= 0) return PA_ERR_BAD_ARG;
+  if (num_tokens == 0) return PA_OK;
+  if (!block_table || !slots) return PA_ERR_BAD_ARG;
+  pa_slot_mapping_kernel<<<(num_tokens + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      block_table, start_pos, num_tokens, block_size, slots);
+  return cudaGetLastError() == cudaSuccess ? PA_OK : PA_ERR_CUDA;
+}
+
+extern "C" int pa_reshape_and_cache(const void* key, const void* value, int64_t kv_stride_token,
+                                    int64_t kv_stride_head, const PaKvCache* cache,
+                                    const int64_t* slot_mapping, int32_t num_tokens, void* stream) {
+  if (!cache || num_tokens < 0) return PA_ERR_BAD_ARG;
+  if (num_tokens == 0) return PA_OK;
+  if (!key || !value || !cache->k || !cache->v || !slot_mapping) return PA_ERR_BAD_ARG;
+  if (cache->dtype != PA_BF16 && cache->dtype != PA_F32) return PA_ERR_UNSUPPORTED;
+  if (cache->head_dim <= 0 || cache->num_kv_heads <= 0 || cache->block_size <= 0 || cache->num_blocks <= 0)
+    return PA_ERR_BAD_ARG;
+  const int es = cache->dtype == PA_F32 ? 4 : 2;
+  RacParams p;
+  p.key = static_cast<const uint8_t*>(key);
+  p.value = static_cast<const uint8_t*>(value);
+  p.k_cache = static_cast<uint8_t*>(cache->k);
+  p.v_cache = static_cast<uint8_t*>(cache->v);
+  p.slots = slot_mapping;
+  p.src_stride_token = kv_stride_token * es;
+  p.src_stride_head = kv_stride_head * es;
+  p.stride_block = cache->stride_block * es;
+  p.stride_head = cache->stride_head * es;
+  p.stride_slot = cache->stride_slot * es;
+  p.num_tokens = num_tokens;
+  p.num_heads = cache->num_kv_heads;
+  p.block_size = cache->block_size;
+  p.num_slots = (int64_t)cache->num_blocks * cache->block_size;
+  const int64_t row_bytes = (int64_t)cache->head_dim * es;
+  const bool vec = aligned16(key) && aligned16(value) && aligned16(cache->k) && aligned16(cache->v) &&
+                   row_bytes % 16 == 0 &&
+                   ((p.src_stride_token | p.src_stride_head | p.stride_block | p.stride_head | p.stride_slot) & 15) == 0;
+  p.row_units = (int32_t)(vec ? row_bytes / 16 : cache->head_dim);
+  const int64_t total = (int64_t)num_tokens * p.num_heads * p.row_units;
+  constexpr int UNROLL = 4;
+  int64_t ctas = (total + 256 * UNROLL - 1) / (256 * UNROLL);
+  if (ctas > 148 * 16) ctas = 148 * 16;                    // grid-stride beyond 16 CTAs per SM
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (vec)
+    pa_reshape_and_cache_kernel<uint4, UNROLL><<<(int)ctas, 256, 0, st>>>(p);
+  else if (es == 4)
+    pa_reshape_and_cache_kernel<uint32_t, UNROLL><<<(int)ctas, 256, 0, st>>>(p);
+  else
+    pa_reshape_and_cache_kernel<uint16_t, UNROLL><<<(int)ctas, 256, 0, st>>>(p);
+  return cudaGetLastError() == cudaSuccess ? PA_OK : PA_ERR_CUDA;
+}
+
+extern "C" int pa_copy_blocks(void* base, int64_t plane_stride_bytes, int32_t num_planes,
+                              int64_t block_stride_bytes, int64_t block_bytes, const int64_t* pairs,
+                              int32_t num_pairs, void* stream) {
+  if (num_pairs < 0 || num_planes < 0 || block_bytes < 0) return PA_ERR_BAD_ARG;
+  if (num_pairs == 0 || num_planes == 0 || block_bytes == 0) return PA_OK;
+  if (!base || !pairs) return PA_ERR_BAD_ARG;
+  if (!aligned16(base) || ((plane_stride_bytes | block_stride_bytes | block_bytes) & 15)) return PA_ERR_MISALIGNED;
+  if (num_pairs > 65535 || num_planes > 65535) return PA_ERR_UNSUPPORTED;
+  dim3 grid((unsigned)((block_bytes + kCopyChunk - 1) / kCopyChunk), (unsigned)num_pairs, (unsigned)num_planes);
+  pa_copy_blocks_kernel<<<grid, kCopyThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<uint8_t*>(base), plane_stride_bytes, block_stride_bytes, block_bytes, pairs);
+  return cudaGetLastError() == cudaSuccess ? PA_OK : PA_ERR_CUDA;
+}
+
+extern "C" int pa_swap_blocks(void* dst_base, int64_t dst_plane_stride_bytes, int64_t dst_block_stride_bytes,
+                              const void* src_base, int64_t src_plane_stride_bytes, int64_t src_block_stride_bytes,
+                              int32_t num_planes, int64_t block_bytes, const int64_t* pairs_host,
+                              int32_t num_pairs, int32_t direction, void* stream) {
+  if (num_pairs < 0 || num_planes < 0 || block_bytes < 0) return PA_ERR_BAD_ARG;
+  if (num_pairs == 0 || num_planes == 0 || block_bytes == 0) return PA_OK;
+  if (!dst_base || !src_base || !pairs_host) return PA_ERR_BAD_ARG;
+  if (direction != 0 && direction != 1) return PA_ERR_BAD_ARG;
+  const cudaMemcpyKind kind = direction == 0 ? cudaMemcpyDeviceToHost : cudaMemcpyHostToDevice;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  uint8_t* dst = static_cast<uint8_t*>(dst_base);
+  const uint8_t* src = static_cast<const uint8_t*>(src_base);
+  // Blocks that are consecutive on both sides (and dense: stride == bytes) travel as one run;
+  // all planes of a run go in ONE strided 2-D copy when the pitches allow it.
+  const bool dense = dst_block_stride_bytes == block_bytes && src_block_stride_bytes == block_bytes;
+  const int64_t kMaxPitch = 0x7fffffff;   // cudaMemcpy2D pitch limit (cudaDevAttrMaxPitch)
+  int i = 0;
+  while (i < num_pairs) {
+    int j = i + 1;
+    if (dense)
+      while (j < num_pairs && pairs_host[2 * j] == pairs_host[2 * (j - 1)] + 1 &&
+             pairs_host[2 * j + 1] == pairs_host[2 * (j - 1) + 1] + 1)
+        ++j;
+    const int64_t width = (int64_t)(j - i) * block_bytes;
+    const uint8_t* s0 = src + pairs_host[2 * i] * src_block_stride_bytes;
+    uint8_t* d0 = dst + pairs_host[2 * i + 1] * dst_block_stride_bytes;
+    cudaError_t e = cudaSuccess;
+    if (num_planes > 1 && dst_plane_stride_bytes <= kMaxPitch && src_plane_stride_bytes <= kMaxPitch &&
+        dst_plane_stride_bytes >= width && src_plane_stride_bytes >= width) {
+      e = cudaMemcpy2DAsync(d0, (size_t)dst_plane_stride_bytes, s0, (size_t)src_plane_stride_bytes, (size_t)width,
+                            (size_t)num_planes, kind, st);
+    } else {
+      for (int pl = 0; pl < num_planes && e == cudaSuccess; ++pl)
+        e = cudaMemcpyAsync(d0 + pl * dst_plane_stride_bytes, s0 + pl * src_plane_stride_bytes, (size_t)width, kind, st);
+    }
+    if (e != cudaSuccess) return PA_ERR_CUDA;
+    i = j;
+  }
+  return PA_OK;
+}

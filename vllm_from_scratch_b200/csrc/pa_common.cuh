@@ -1,0 +1,140 @@
+// Shared device-side definitions for the paged-attention kernels (sm_100a).
+//
+// Work decomposition ("stream-K over KV blocks"):
+//   The decode batch is flattened into one linear space of KV blocks,
+//       L = cum[s] * HS + hseg * nblk(s) + b
+//   (s = sequence, hseg = head segment of that sequence, b = logical block,
+//    cum[s] = sum of nblk over earlier sequences, HS = head segments per
+//    sequence).  The space is cut into `num_workers` equal contiguous ranges of
+//   Q blocks; one persistent WARP ("worker") streams each range.  A range may
+//   start / end inside a (sequence, head) segment, so a worker emits one partial
+//   (unnormalised O, running max m, running sum l) per segment it touches, into
+//   partial slot `segment_id + worker_id` (strictly increasing along the linear
+//   order, hence unique; at most num_segments + num_workers slots).  Segments
+//   that lie inside a single worker are normalised and written directly.  The
+//   reduce kernel merges the partials of split segments.
+//   This keeps every worker's byte count equal for ragged batches, which is what
+//   an HBM-bound kernel needs to finish all SMs at the same time.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define PA_MIN_BLOCKS_PER_WORKER 4
+#define PA_MAX_BATCH_SMEM 8191   // cum[] lives in shared memory: (B + 1) * 4 bytes
+
+struct PaDecodeParams {
+  const void* q;
+  void* out;
+  const void* k;
+  const void* v;
+  const int32_t* block_tables;
+  const int32_t* seq_lens;
+  int64_t q_stride_b, q_stride_h;
+  int64_t o_stride_b, o_stride_h;
+  int64_t kv_stride_block, kv_stride_head, kv_stride_slot;
+  int32_t bt_stride;
+  int32_t batch, num_q_heads, num_kv_heads, head_dim, block_size;
+  int32_t group;          // g = Hq / Hkv
+  int32_t tile_q;         // q heads per head segment (partial rows per slot)
+  int32_t q_tiles;        // ceil(g / tile_q); HS = Hkv * q_tiles
+  int32_t num_workers;
+  int32_t pos_head, pos_block;   // TMA coordinate positions (1..3) of the head / block dims
+  float scale_log2e;      // (1 / sqrt(D)) * log2(e)
+  // workspace
+  float* part_o;          // [slots][tile_q][D]
+  float2* part_ml;        // [slots][tile_q]  (m in log2 domain, l)
+  int32_t* plan;          // [0] = Q, [1] = total linear blocks, [2 .. 2 + B] = cum[0..B]
+};
+
+struct PaCursor {
+  int s;      // sequence
+  int h;      // head segment within the sequence
+  int b;      // logical block within the sequence
+  int n;      // nblk(s)
+};
+
+__device__ __forceinline__ int pa_ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// CTA-wide exclusive scan of nblk(s) into s_cum[0..B]; every thread of the CTA must call.
+// scratch: >= 33 ints of shared memory.
+__device__ __forceinline__ void pa_build_cum(const int32_t* __restrict__ seq_lens, int batch,
+                                             int block_size, int* s_cum, int* scratch) {
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int lane = tid & 31, warp = tid >> 5, nwarps = (nthr + 31) >> 5;
+  const int per = pa_ceil_div(batch, nthr);
+  const int lo = min(tid * per, batch), hi = min(lo + per, batch);
+  int sum = 0;
+  for (int i = lo; i < hi; ++i) sum += pa_ceil_div(max(__ldg(seq_lens + i), 0), block_size);
+  int incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) scratch[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int w = lane < nwarps ? scratch[lane] : 0;
+    int wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, wi, o);
+      if (lane >= o) wi += t;
+    }
+    scratch[lane] = wi - w;    // exclusive prefix of warp sums
+    if (lane == 31) scratch[32] = wi;
+  }
+  __syncthreads();
+  int run = scratch[warp] + incl - sum;
+  for (int i = lo; i < hi; ++i) {
+    s_cum[i] = run;
+    run += pa_ceil_div(max(__ldg(seq_lens + i), 0), block_size);
+  }
+  if (tid == 0) s_cum[batch] = scratch[32];
+  __syncthreads();
+}
+
+// Map a linear block index to (s, h, b).  s_cum is in shared memory.
+__device__ __forceinline__ PaCursor pa_locate(const int* s_cum, int batch, int hs, int lin) {
+  const int key = lin / hs;
+  int lo = 0, hi = batch;          // find largest s with s_cum[s] <= key and s_cum[s + 1] > key
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (s_cum[mid] <= key) lo = mid; else hi = mid;
+  }
+  // lo is the LAST index with s_cum[lo] <= key, so s_cum[lo + 1] > key: the sequence is non-empty.
+  PaCursor c;
+  c.s = lo;
+  c.n = s_cum[lo + 1] - s_cum[lo];
+  const int r = lin - s_cum[lo] * hs;
+  c.h = r / c.n;
+  c.b = r - c.h * c.n;
+  return c;
+}
+
+__device__ __forceinline__ void pa_advance(PaCursor& c, const int* s_cum, int batch, int hs) {
+  if (++c.b < c.n) return;
+  c.b = 0;
+  if (++c.h < hs) return;
+  c.h = 0;
+  do {
+    ++c.s;
+    if (c.s >= batch) { c.n = 1; return; }     // past the end; never dereferenced
+    c.n = s_cum[c.s + 1] - s_cum[c.s];
+  } while (c.n == 0);
+}
+
+__device__ __forceinline__ float pa_to_float(float x) { return x; }
+__device__ __forceinline__ float pa_to_float(__nv_bfloat16 x) { return __bfloat162float(x); }
+__device__ __forceinline__ void pa_store(float* p, float x) { *p = x; }
+__device__ __forceinline__ void pa_store(__nv_bfloat16* p, float x) { *p = __float2bfloat16_rn(x); }
+
+// host-side launchers implemented by the individual translation units
+struct PaKvCache;
+int pa_launch_decode_tma(const PaDecodeParams& p, int num_sms, cudaStream_t stream);
+int pa_launch_decode_generic(const PaDecodeParams& p, int dtype, int ctas, cudaStream_t stream);
+int pa_launch_reduce(const PaDecodeParams& p, int dtype, cudaStream_t stream);
+bool pa_decode_tma_supported(const PaDecodeParams& p, int dtype);
+int pa_decode_tma_workers(int num_sms);
+int pa_decode_generic_workers(int num_sms, int* ctas);
