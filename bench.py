@@ -1,0 +1,471 @@
+#!/usr/bin/env python
+"""bench.py - paged-attention decode tokens/s and KV-read GB/s on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2|c3|c5]
+
+A "step" is one pass of the hot path over one decode batch: ONE attention-layer call
+(split-K decode kernel + cross-partition reduce) for every sequence of the batch.  At N = 1
+the workload is BASELINE.json configs[1] ("C2": 64 seqs x 2k context, 32 Q / 8 KV heads,
+head_dim 128, bf16, block_size 16).  For N > 1 the batch is sharded by sequence: every rank
+owns its own block pool and block tables and runs the same per-GPU batch (weak scaling, no
+data-path collective); value = sequences all ranks advanced / max-over-ranks device time.
+
+L2: the timed loop rotates over `--layers` per-layer caches of the pool (C2: 8 x 512 MiB =
+4 GiB >> 126 MB L2), i.e. inputs larger than L2; nothing is re-read from cache.
+
+One JSON line on stdout (rank 0).  `--impl reference` times the CPU oracle port of the
+reference's own algorithm (oracle/paged_attention_oracle.py::decode_loop) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "paged_attn_decode_tokens_per_s"
+UNIT = "tokens/s"
+NOMINAL_HBM_GBS = 8000.0          # the metric is quoted against 8 TB/s (BASELINE.json)
+FALLBACK_HBM_GBS = 6650.0         # /opt/skills/guides/B200_PROFILING.md fallback
+
+WORKLOADS = {
+    # name: (seqs per GPU, context, Hq, Hkv, D, BS, default layers, description)
+    "c2": (64, 2048, 32, 8, 128, 16, 8,
+           "C2 Llama-3-8B-shaped decode: 64 seqs x 2048 ctx, 32 Q / 8 KV heads, head_dim 128, bf16, block_size 16"),
+    "c3": (8, 32768, 32, 8, 128, 16, 4,
+           "C3 long-context decode: 8 seqs x 32768 ctx, GQA 32/8, head_dim 128, bf16, block_size 16"),
+    "c5": (64, 8192, 32, 8, 128, 16, 2,
+           "C5 shard: 64 seqs x 8192 ctx per GPU (512 seqs over 8 GPUs), GQA 32/8, head_dim 128, bf16"),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--layers", type=int, default=0, help="per-layer caches the loop rotates over")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (default min(steps, 300))")
+    ap.add_argument("--ramp-ms", type=float, default=300.0, help="untimed clock ramp before the warm-up steps")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------
+# clocks sampling during the timed region
+# ---------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU every few ms through NVML."""
+
+    REASONS = {
+        0x0000000000000004: "sw_power_cap",
+        0x0000000000000008: "hw_slowdown",
+        0x0000000000000020: "sw_thermal_slowdown",
+        0x0000000000000040: "hw_thermal_slowdown",
+        0x0000000000000080: "hw_power_brake_slowdown",
+    }
+
+    def __init__(self, index: int, period_s: float = 0.002):
+        super().__init__(daemon=True)
+        self.index = index
+        self.period = period_s
+        self.samples = []          # (t, sm_mhz, reasons_mask, power_w)
+        self.sm_max = None
+        self.stop_flag = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(index))
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:      # noqa: BLE001 - clocks are advisory; report the failure in JSON
+            self.err = repr(e)
+
+    @staticmethod
+    def _physical_index(i: int) -> int:
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [x for x in vis.split(",") if x.strip() != ""]
+            try:
+                return int(ids[i])
+            except (ValueError, IndexError):
+                return i
+        return i
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self.stop_flag.is_set():
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:   # noqa: BLE001
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                try:
+                    pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                except Exception:   # noqa: BLE001
+                    pw = None
+                self.samples.append((time.perf_counter(), mhz, mask, pw))
+            except Exception:       # noqa: BLE001
+                pass
+            time.sleep(self.period)
+
+    def summary(self, t0: float, t1: float) -> dict:
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "error": getattr(self, "err", "nvml unavailable")}
+        inside = [s for s in self.samples if t0 <= s[0] <= t1]
+        where = "timed_region"
+        if not inside:              # region shorter than the sampling period: nearest samples
+            inside = sorted(self.samples, key=lambda s: abs(s[0] - t1))[:3]
+            where = "nearest_to_timed_region"
+        mask = 0
+        for s in inside:
+            mask |= s[2]
+        reasons = [name for bit, name in self.REASONS.items() if mask & bit]
+        pws = [s[3] for s in inside if s[3] is not None]
+        return {"sm_mhz": statistics.median(s[1] for s in inside) if inside else None,
+                "sm_max_mhz": self.sm_max, "reasons": reasons, "samples": len(inside), "where": where,
+                "power_w_max": max(pws) if pws else None}
+
+
+# ---------------------------------------------------------------------------------------
+# workload
+# ---------------------------------------------------------------------------------------
+def algorithmic_bytes(b, ctx, hq, hkv, d, bs, esize=2):
+    kv = b * 2 * ctx * hkv * d * esize
+    io = b * hq * d * esize * 2 + b * ((ctx + bs - 1) // bs) * 4 + b * 4
+    return kv, io
+
+
+def peak_hbm():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy read+write)"
+        except Exception:           # noqa: BLE001
+            pass
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(workload: str):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(workload)
+        except Exception:           # noqa: BLE001
+            return None
+    return None
+
+
+def make_workload(torch, dev, wl, layers, seed):
+    """Synthetic KV pool [2, L, NB, Hkv, BS, D] (reference layout, paged_attention.py:26-30), fully
+    scattered block tables (rows of a seeded randperm; no two sequences share a block)."""
+    from vllm_from_scratch_b200 import paged_attention as P
+    b, ctx, hq, hkv, d, bs = wl[:6]
+    nblk = (ctx + bs - 1) // bs
+    nb = b * nblk + 64
+    pool = P.KVCachePool(nb, bs, hkv, d, layers, dtype=torch.bfloat16, device=dev)
+    g = torch.Generator(device=dev).manual_seed(seed)
+    flat = pool.kv_cache.view(-1)
+    chunk = 1 << 28
+    for lo in range(0, flat.numel(), chunk):        # fill in pieces: no 2x fp32 temporary of the pool
+        n = min(chunk, flat.numel() - lo)
+        flat[lo:lo + n] = torch.randn(n, generator=g, device=dev, dtype=torch.float32).to(torch.bfloat16)
+    gc = torch.Generator().manual_seed(seed)
+    perm = torch.randperm(nb, generator=gc)[: b * nblk].to(torch.int32).view(b, nblk)
+    lens = torch.full((b,), ctx, dtype=torch.int32)
+    q = torch.randn(b, hq, d, generator=gc).to(torch.bfloat16)
+    k_new = torch.randn(b, hkv, d, generator=gc).to(torch.bfloat16)
+    v_new = torch.randn(b, hkv, d, generator=gc).to(torch.bfloat16)
+    pos = lens.long() - 1
+    slots = perm.long()[torch.arange(b), pos // bs] * bs + pos % bs
+    return pool, perm, lens, q, k_new, v_new, slots
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from vllm_from_scratch_b200 import _lib, paged_attention as P
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (impl=ours) needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+
+    wl = WORKLOADS[args.workload]
+    b, ctx, hq, hkv, d, bs, def_layers, desc = wl
+    layers = args.layers or def_layers
+    pool, bts_h, lens_h, q_h, k_h, v_h, slots_h = make_workload(torch, dev, wl, layers, seed=1234 + rank)
+    bts, lens, q = bts_h.to(dev), lens_h.to(dev), q_h.to(dev)
+    out = torch.empty_like(q)
+    ws = torch.empty(P.decode_workspace_bytes(b, hq, hkv, d), dtype=torch.uint8, device=dev)
+    caches = [pool.layer(i) for i in range(layers)]
+    kv_bytes, io_bytes = algorithmic_bytes(b, ctx, hq, hkv, d, bs)
+
+    def step(i):
+        P.paged_attention_decode_batched(q, caches[i % layers], bts, lens, out=out, workspace=ws)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    # untimed: ramp clocks, fault in the tensor maps, then the W warm-up steps
+    t_end = time.perf_counter() + args.ramp_ms * 1e-3
+    i = 0
+    while time.perf_counter() < t_end:
+        step(i)
+        i += 1
+        if i % 64 == 0:
+            torch.cuda.synchronize()
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    torch.cuda.synchronize()
+
+    # ---- timed region: K steps, device time, max over ranks --------------------------------
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(args.steps):
+        step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.summary(t0, t1)
+
+    # ---- per-kernel durations (roofline): same steps with events around each kernel -----------
+    nprof = min(args.steps, 512)
+    lib.pa_profile_begin(nprof)
+    for i in range(nprof):
+        step(i)
+    import ctypes
+    dec_ms = (ctypes.c_float * nprof)()
+    red_ms = (ctypes.c_float * nprof)()
+    got = lib.pa_profile_end(dec_ms, red_ms, nprof)
+    if got <= 0:
+        raise RuntimeError(f"pa_profile_end returned {got}")
+    dec_avg = sum(dec_ms[:got]) / got
+    red_avg = sum(red_ms[:got]) / got
+
+    # ---- e2e: host buffers in, host buffer out, through the public Python API ----------------
+    ne2e = args.e2e_steps or min(args.steps, 300)
+    pin = lambda t: t.contiguous().pin_memory()     # noqa: E731
+    q_p, k_p, v_p, s_p, bt_p, ln_p = pin(q_h), pin(k_h), pin(v_h), pin(slots_h), pin(bts_h), pin(lens_h)
+    out_p = torch.empty(q_h.shape, dtype=q_h.dtype).pin_memory()
+    q_d, k_d, v_d = torch.empty_like(q), torch.empty_like(k_h, device=dev), torch.empty_like(v_h, device=dev)
+    s_d, bt_d, ln_d = torch.empty_like(slots_h, device=dev), torch.empty_like(bts), torch.empty_like(lens)
+    h2d = sum(t.numel() * t.element_size() for t in (q_p, k_p, v_p, s_p, bt_p, ln_p))
+    d2h = out_p.numel() * out_p.element_size()
+
+    def e2e_step(i):
+        q_d.copy_(q_p, non_blocking=True)
+        k_d.copy_(k_p, non_blocking=True)
+        v_d.copy_(v_p, non_blocking=True)
+        s_d.copy_(s_p, non_blocking=True)
+        bt_d.copy_(bt_p, non_blocking=True)
+        ln_d.copy_(ln_p, non_blocking=True)
+        cache = caches[i % layers]
+        P.reshape_and_cache(k_d, v_d, cache, s_d)                    # this step's KV slot write
+        P.paged_attention_decode_batched(q_d, cache, bt_d, ln_d, out=out, workspace=ws)
+        out_p.copy_(out, non_blocking=True)
+        torch.cuda.synchronize()                                      # the caller reads out_p now
+
+    for i in range(5):
+        e2e_step(i)
+    barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(ne2e):
+        e2e_step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    barrier()
+    ms_e2e = e0.elapsed_time(e1)
+    sampler.stop_flag.set()
+
+    if world > 1:
+        t = torch.tensor([ms_total, ms_e2e, dec_avg, red_avg], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, ms_e2e, dec_avg, red_avg = t.tolist()
+    ms_step = ms_total / args.steps
+    value = world * b / (ms_step * 1e-3)
+    e2e_value = world * b / (ms_e2e / ne2e * 1e-3)
+    kv_gbs = world * kv_bytes / (ms_step * 1e-3) / 1e9
+    peak, peak_src = peak_hbm()
+    achieved = (kv_bytes + io_bytes) / (dec_avg * 1e-3) / 1e9
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": desc, "seqs_per_gpu": b, "context": ctx, "num_q_heads": hq, "num_kv_heads": hkv,
+                   "head_dim": d, "block_size": bs, "kv_layout": "[2, L, NB, Hkv, BS, D] (reference pool)",
+                   "block_tables": "seeded randperm, fully scattered",
+                   "parallelism": f"sequence-sharded x{world}, one pool per GPU, no collective",
+                   "l2": f"inputs larger than L2: loop rotates over {layers} per-layer caches of "
+                         f"{kv_bytes / 2**20:.0f} MiB each",
+                   "step": "one attention-layer decode call (split-K kernel + reduce kernel) over the batch"},
+        "kv_read_gbs": kv_gbs, "kv_read_gbs_per_gpu": kv_gbs / world,
+        "pct_of_8tbs_per_gpu": 100.0 * kv_gbs / world / NOMINAL_HBM_GBS,
+        "kv_bytes_per_step_per_gpu": kv_bytes,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
+                     "kernel": "pa_decode_tma_kernel<128,1>", "kernel_ms": dec_avg, "reduce_kernel_ms": red_avg,
+                     "algorithmic_bytes_per_launch": kv_bytes + io_bytes,
+                     "frac_of_nominal_8tbs": achieved / NOMINAL_HBM_GBS, "launches_timed": got},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": ne2e, "ms_per_step": ms_e2e / ne2e,
+                "what": "pinned host q/k/v/slots/block tables/seq lens -> H2D -> reshape_and_cache -> decode -> "
+                        "D2H out, synchronised every step; the KV pool is resident state"},
+        "gpu_launches": 2 * args.steps,
+        "clocks": clocks,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(torch, pool.kv_cache[:, 0].cpu(), bts_h, lens_h, q_h, wl, args.cpu_seconds)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------
+# CPU legs: the oracle port of the reference algorithm (oracle/ is the checker / baseline only)
+# ---------------------------------------------------------------------------------------
+def cpu_model_name():
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("model name"):
+                return ln.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def cpu_baseline(torch, kv_layer_cpu, bts, lens, q, wl, budget_s):
+    """Reference algorithm as shipped (row-by-row gather through the block table, then einsum /
+    softmax / einsum in bf16: oracle decode_loop = paged_attention.py:80-101) on ONE host thread
+    (it is interpreter-bound), on a bounded sample of the same batch; plus the vectorised
+    restatement on all cores for a fairer CPU number."""
+    from oracle import paged_attention_oracle as O
+    b, ctx, hq, hkv, d, bs = wl[:6]
+    t0 = time.perf_counter()
+    done = 0
+    while done < b and (time.perf_counter() - t0 < budget_s or done == 0):
+        O.decode_loop(q[done], kv_layer_cpu, bts[done].tolist(), int(lens[done]), d, hq, hkv, bs)
+        done += 1
+    dt = time.perf_counter() - t0
+    tv0 = time.perf_counter()
+    nvec = 0
+    while nvec < b and (time.perf_counter() - tv0 < 3.0 or nvec == 0):
+        O.decode_vectorised(q[nvec], kv_layer_cpu, bts[nvec].tolist(), int(lens[nvec]), d, hq, hkv, bs,
+                            compute_dtype=torch.float32)
+        nvec += 1
+    dtv = time.perf_counter() - tv0
+    return {"value": done / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"{done} of {b} sequences of the same batch (ctx {ctx}), oracle decode_loop, bf16, "
+                      f"{dt:.1f} s; sequences are independent so tokens/s = sequences / time",
+            "cpu_model": cpu_model_name(), "host_cores": os.cpu_count(),
+            "vectorised_port": {"value": nvec / dtv, "unit": UNIT, "cores": torch.get_num_threads(),
+                                "sample": f"{nvec} sequences, oracle decode_vectorised fp32, {dtv:.1f} s"}}
+
+
+_REF_STATE = {}
+
+
+def _ref_worker(idx):
+    from oracle import paged_attention_oracle as O
+    s = _REF_STATE
+    b, ctx, hq, hkv, d, bs = s["wl"][:6]
+    O.decode_loop(s["q"][idx], s["kv"], s["bts"][idx].tolist(), ctx, d, hq, hkv, bs)
+    return idx
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU algorithm (oracle port, decode_loop) on all host
+    cores - one process per core, one sequence per process per step (sequences are independent)."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+
+    import torch
+    torch.set_num_threads(1)
+    wl = WORKLOADS[args.workload]
+    b, ctx, hq, hkv, d, bs, _, desc = wl
+    cores = max(1, min(os.cpu_count() or 1, b, 64))
+    nseq = cores                                   # sample: one sequence per core per step
+    nblk = (ctx + bs - 1) // bs
+    nb = nseq * nblk + 8
+    g = torch.Generator().manual_seed(1234)
+    kv = torch.randn(2, nb, hkv, bs, d, generator=g).to(torch.bfloat16)
+    bts = torch.randperm(nb, generator=g)[: nseq * nblk].to(torch.int32).view(nseq, nblk)
+    q = torch.randn(nseq, hq, d, generator=g).to(torch.bfloat16)
+    _REF_STATE.update(wl=wl, kv=kv, bts=bts, q=q)
+    # keep the whole run within a few minutes: ~0.5-1.5 s per step
+    steps = min(args.steps, 20)
+    warmup = min(max(args.warmup, 1), 2)
+    ctxmp = mp.get_context("fork")
+    with ctxmp.Pool(cores) as pool:
+        for _ in range(warmup):
+            pool.map(_ref_worker, range(nseq), chunksize=1)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            pool.map(_ref_worker, range(nseq), chunksize=1)
+        dt = time.perf_counter() - t0
+    value = nseq * steps / dt
+    kv_bytes, _ = algorithmic_bytes(nseq, ctx, hq, hkv, d, bs)
+    sample = (f"each step = {nseq} of the batch's {b} sequences (ctx {ctx}), one per process on {cores} cores, "
+              f"oracle decode_loop in bf16; {steps} steps (capped from {args.steps} to bound the run)")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": desc, "seqs_per_gpu": b, "context": ctx, "num_q_heads": hq, "num_kv_heads": hkv,
+                   "head_dim": d, "block_size": bs, "note": "CPU arm: runs on rank 0's host cores only"},
+        "kv_read_gbs": kv_bytes * steps / dt / 1e9,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "cpu_model": cpu_model_name(), "host_cores": os.cpu_count()},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

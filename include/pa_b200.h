@@ -162,6 +162,14 @@ int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
  * decode kernel even for shapes the TMA kernel takes.  Returns the old value. */
 int pa_decode_force_path(int path);
 
+/* ---- per-kernel device timing (bench.py's roofline line) ---------------------
+ * pa_profile_begin(n): the next n pa_decode calls record CUDA events on their
+ * stream before the split-K kernel, between it and the reduce kernel, and after.
+ * pa_profile_end: synchronises on those events, writes the per-call durations
+ * (milliseconds) and returns how many calls were recorded (<0 on error).        */
+int pa_profile_begin(int32_t max_calls);
+int pa_profile_end(float* decode_ms_host, float* reduce_ms_host, int32_t capacity);
+
 #ifdef __cplusplus
 }
 #endif

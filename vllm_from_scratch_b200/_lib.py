@@ -50,6 +50,8 @@ SIGNATURES = {
     "pa_prefill_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
     "pa_prefill": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
                            c_void_p, c_int32, c_int32, c_int32, c_void_p, c_size_t, c_void_p]),
+    "pa_profile_begin": (c_int, [c_int32]),
+    "pa_profile_end": (c_int, [c_void_p, c_void_p, c_int32]),
 }
 
 _lib = None

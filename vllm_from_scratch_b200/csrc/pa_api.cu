@@ -4,6 +4,8 @@
 // current stream.
 #include <atomic>
 #include <math.h>
+#include <mutex>
+#include <vector>
 
 #include "../../include/pa_b200.h"
 #include "pa_common.cuh"
@@ -38,6 +40,15 @@ WsLayout ws_layout(int batch, int64_t slots, int rows, int head_dim) {
   w.total = w.o_off + align_up((size_t)slots * rows * head_dim * sizeof(float), 256);
   return w;
 }
+
+// Per-kernel device timing for the roofline report (pa_profile_begin / pa_profile_end): three
+// events per pa_decode call - before the split-K kernel, between it and the reduce, after.
+struct ProfState {
+  std::mutex mu;
+  std::vector<cudaEvent_t> ev;     // 3 per call
+  int cap = 0, used = 0;
+  bool on = false;
+} g_prof;
 
 __global__ void pa_iota_lens_kernel(int32_t* lens, int32_t first, int32_t n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -133,9 +144,50 @@ extern "C" int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h, 
   p.part_o = reinterpret_cast<float*>(ws + w.o_off);
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaEvent_t* pe = nullptr;
+  if (g_prof.on) {
+    std::lock_guard<std::mutex> lock(g_prof.mu);
+    if (g_prof.on && g_prof.used < g_prof.cap) pe = &g_prof.ev[3 * g_prof.used++];
+  }
+  if (pe) cudaEventRecord(pe[0], st);
   int rc = tma ? pa_launch_decode_tma(p, sms, st) : pa_launch_decode_generic(p, cache->dtype, ctas, st);
   if (rc) return rc;
-  return pa_launch_reduce(p, cache->dtype, st);
+  if (pe) cudaEventRecord(pe[1], st);
+  rc = pa_launch_reduce(p, cache->dtype, st);
+  if (pe) cudaEventRecord(pe[2], st);
+  return rc;
+}
+
+extern "C" int pa_profile_begin(int32_t max_calls) {
+  if (max_calls <= 0) return PA_ERR_BAD_ARG;
+  std::lock_guard<std::mutex> lock(g_prof.mu);
+  for (cudaEvent_t e : g_prof.ev) cudaEventDestroy(e);
+  g_prof.ev.assign((size_t)3 * max_calls, nullptr);
+  for (auto& e : g_prof.ev)
+    if (cudaEventCreate(&e) != cudaSuccess) return PA_ERR_CUDA;
+  g_prof.cap = max_calls;
+  g_prof.used = 0;
+  g_prof.on = true;
+  return PA_OK;
+}
+
+extern "C" int pa_profile_end(float* decode_ms, float* reduce_ms, int32_t cap) {
+  std::lock_guard<std::mutex> lock(g_prof.mu);
+  g_prof.on = false;
+  int n = g_prof.used < cap ? g_prof.used : cap;
+  int rc = n;
+  for (int i = 0; i < n; ++i) {
+    if (cudaEventSynchronize(g_prof.ev[3 * i + 2]) != cudaSuccess ||
+        cudaEventElapsedTime(decode_ms + i, g_prof.ev[3 * i], g_prof.ev[3 * i + 1]) != cudaSuccess ||
+        cudaEventElapsedTime(reduce_ms + i, g_prof.ev[3 * i + 1], g_prof.ev[3 * i + 2]) != cudaSuccess) {
+      rc = PA_ERR_CUDA;
+      break;
+    }
+  }
+  for (cudaEvent_t e : g_prof.ev) cudaEventDestroy(e);
+  g_prof.ev.clear();
+  g_prof.cap = g_prof.used = 0;
+  return rc;
 }
 
 // ---- prefill = one decode "sequence" per query token over the shared block table --------
