@@ -78,12 +78,19 @@ int pa_decode_num_workers(void);
  * block_tables int32 [batch, bt_stride]; entries beyond ceil(seq_len/BS) are
  *   never dereferenced.  seq_lens int32 [batch]; seq_len == 0 -> zeros.
  * softmax scale is 1/sqrt(D) (paged_attention.py:80).
- * Two launches: the split-K ("flash-decoding") kernel over (sequence, KV head,
- * context partition) work ranges and a small cross-partition reduce kernel.
- * workspace: pa_decode_workspace_bytes() bytes, 16-byte aligned, contents
- *   undefined on entry, owned by the caller.                                 */
+ * Split-K ("flash-decoding") over (sequence, KV head, context partition) work
+ * ranges, followed by a cross-partition merge.
+ * Two launches on the generic path; ONE on the bf16 / block_size 16 fast path,
+ * whose kernel merges its own split-K partials ("last arriver merges").
+ * workspace: pa_decode_workspace_bytes() bytes, 16-byte aligned, owned by the
+ *   caller.  Its first 1 MiB is a counter header that must be ZERO on entry:
+ *   call pa_decode_workspace_init once after allocating it (or memset it);
+ *   every pa_decode / pa_prefill call leaves the header zero again, so the same
+ *   workspace serves any sequence of stream-ordered calls of any shape.  Two
+ *   calls that may run concurrently (different streams) need two workspaces.  */
 size_t pa_decode_workspace_bytes(int32_t batch, int32_t num_q_heads,
                                  int32_t num_kv_heads, int32_t head_dim);
+int pa_decode_workspace_init(void* workspace, size_t workspace_bytes, void* stream);
 
 int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h,
               void* out, int64_t o_stride_b, int64_t o_stride_h,
@@ -161,6 +168,13 @@ int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
  * 0 = automatic kernel choice (default); 1 = force the generic CUDA-core
  * decode kernel even for shapes the TMA kernel takes.  Returns the old value. */
 int pa_decode_force_path(int path);
+/* Split-K plan of the fast path: the last 1 / pool_div of the KV blocks is handed out
+ * dynamically in chunks of >= chunk_min blocks (pool_div = 0: static split only).      */
+int pa_decode_set_tuning(int pool_div, int chunk_min);
+/* Debug: when non-null, every fast-path worker (warp) writes 6 int64 to
+ * device_buffer[6 * worker]: SM id, start / end-of-static-range / end timestamps (ns),
+ * blocks in its static range, blocks in total.  pa_decode_num_workers() entries.      */
+int pa_decode_debug_times(void* device_buffer);
 
 /* ---- per-kernel device timing (bench.py's roofline line) ---------------------
  * pa_profile_begin(n): the next n pa_decode calls record CUDA events on their

@@ -13,6 +13,8 @@
 namespace {
 
 std::atomic<int> g_force_path{0};
+std::atomic<int> g_pool_div{4}, g_chunk_min{4};
+std::atomic<long long*> g_dbg{nullptr};
 
 int sm_count() {
   static std::atomic<int> cached[64];
@@ -31,11 +33,15 @@ struct WsLayout {
   size_t plan_off, ml_off, o_off, total;
 };
 
-// rows = partial rows per slot (tile_q), slots = segments + workers.
+// The workspace starts with a fixed-size counter header that must be zero when pa_decode is
+// entered and is zero again when it returns (pa_decode_workspace_init zeroes it once).
+constexpr size_t kHeaderBytes = 1 << 20;
+
+// rows = partial rows per slot, slots = partial slots.
 WsLayout ws_layout(int batch, int64_t slots, int rows, int head_dim) {
   WsLayout w;
-  w.plan_off = 0;
-  w.ml_off = align_up((size_t)(batch + 3) * 4, 256);
+  w.plan_off = kHeaderBytes;
+  w.ml_off = w.plan_off + align_up((size_t)(batch + 3) * 4, 256);
   w.o_off = w.ml_off + align_up((size_t)slots * rows * sizeof(float2), 256);
   w.total = w.o_off + align_up((size_t)slots * rows * head_dim * sizeof(float), 256);
   return w;
@@ -49,6 +55,21 @@ struct ProfState {
   int cap = 0, used = 0;
   bool on = false;
 } g_prof;
+
+// TMA path partial slots: one per (segment, range) + one per (segment, chunk group)
+int64_t tma_slots(int batch, int num_kv_heads, int sms) {
+  const int64_t segs = (int64_t)batch * num_kv_heads;
+  const int nc_max = pa_decode_tma_nc_max(sms);
+  const int ng_max = (nc_max + pa_decode_tma_group() - 1) / pa_decode_tma_group();
+  return 2 * segs + pa_decode_tma_workers(sms) + nc_max + ng_max;
+}
+
+bool tma_header_fits(int batch, int num_kv_heads, int sms) {
+  const int64_t segs = (int64_t)batch * num_kv_heads;
+  const int nc_max = pa_decode_tma_nc_max(sms);
+  const int ng_max = (nc_max + pa_decode_tma_group() - 1) / pa_decode_tma_group();
+  return (size_t)(pa_decode_tma_header_ints() + 2 * segs + ng_max) * 4 <= kHeaderBytes;
+}
 
 __global__ void pa_iota_lens_kernel(int32_t* lens, int32_t first, int32_t n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -74,6 +95,18 @@ extern "C" const char* pa_status_string(int status) {
 
 extern "C" int pa_decode_force_path(int path) { return g_force_path.exchange(path); }
 
+extern "C" int pa_decode_set_tuning(int pool_div, int chunk_min) {
+  if (pool_div < 0 || pool_div == 1 || chunk_min < 1) return PA_ERR_BAD_ARG;
+  g_pool_div.store(pool_div);
+  g_chunk_min.store(chunk_min);
+  return PA_OK;
+}
+
+extern "C" int pa_decode_debug_times(void* device_buffer) {
+  g_dbg.store(static_cast<long long*>(device_buffer));
+  return PA_OK;
+}
+
 extern "C" int pa_decode_num_workers(void) {
   const int sms = sm_count();
   if (sms <= 0) return PA_ERR_NO_DEVICE;
@@ -82,17 +115,23 @@ extern "C" int pa_decode_num_workers(void) {
 
 extern "C" size_t pa_decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
                                             int32_t head_dim) {
-  if (batch <= 0 || num_q_heads <= 0 || num_kv_heads <= 0 || head_dim <= 0) return 256;
+  if (batch <= 0 || num_q_heads <= 0 || num_kv_heads <= 0 || head_dim <= 0) return kHeaderBytes;
   int sms = sm_count();
   if (sms <= 0) sms = 148;                       // sizing without a device: assume a B200
   const int g = (num_q_heads + num_kv_heads - 1) / num_kv_heads;
   const int nt = (g + 7) / 8;
   int ctas;
-  const int64_t slots_tma = (int64_t)batch * num_kv_heads + pa_decode_tma_workers(sms);
+  const int64_t slots_tma = tma_slots(batch, num_kv_heads, sms);
   const int64_t slots_gen = (int64_t)batch * num_kv_heads * nt + pa_decode_generic_workers(sms, &ctas);
-  const size_t a = ws_layout(batch, slots_tma, 8 * nt, head_dim).total;
+  const size_t a = ws_layout(batch, slots_tma, g, head_dim).total;
   const size_t b = ws_layout(batch, slots_gen, 8, head_dim).total;
   return a > b ? a : b;
+}
+
+extern "C" int pa_decode_workspace_init(void* workspace, size_t workspace_bytes, void* stream) {
+  if (!workspace || workspace_bytes < kHeaderBytes) return PA_ERR_WORKSPACE;
+  return cudaMemsetAsync(workspace, 0, kHeaderBytes, static_cast<cudaStream_t>(stream)) == cudaSuccess ? PA_OK
+                                                                                                        : PA_ERR_CUDA;
 }
 
 extern "C" int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h, void* out, int64_t o_stride_b,
@@ -124,21 +163,33 @@ extern "C" int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h, 
   p.pos_head = p.pos_block = 0;
   p.scale_log2e = (float)((1.0 / sqrt((double)D)) * 1.4426950408889634);
 
-  const bool tma = g_force_path.load() != 1 && pa_decode_tma_supported(p, cache->dtype);
+  const bool tma = g_force_path.load() != 1 && pa_decode_tma_supported(p, cache->dtype) &&
+                   tma_header_fits(batch, Hkv, sms);
   int ctas = 0;
+  int64_t slots;
+  int rows;
+  p.nc_max = 0;
+  p.pool_div = g_pool_div.load();
+  p.chunk_min = g_chunk_min.load();
+  p.dbg = g_dbg.load();
   if (tma) {
     p.tile_q = 8 * ((p.group + 7) / 8);
     p.q_tiles = 1;
     p.num_workers = pa_decode_tma_workers(sms);
+    p.nc_max = pa_decode_tma_nc_max(sms);
+    slots = tma_slots(batch, Hkv, sms);
+    rows = p.group;
   } else {
     p.tile_q = 8;
     p.q_tiles = (p.group + 7) / 8;
     p.num_workers = pa_decode_generic_workers(sms, &ctas);
+    slots = (int64_t)batch * Hkv * p.q_tiles + p.num_workers;
+    rows = p.tile_q;
   }
-  const int64_t slots = (int64_t)batch * Hkv * p.q_tiles + p.num_workers;
-  const WsLayout w = ws_layout(batch, slots, p.tile_q, D);
+  const WsLayout w = ws_layout(batch, slots, rows, D);
   if (workspace_bytes < w.total) return PA_ERR_WORKSPACE;
   uint8_t* ws = static_cast<uint8_t*>(workspace);
+  p.counters = reinterpret_cast<int32_t*>(ws);
   p.plan = reinterpret_cast<int32_t*>(ws + w.plan_off);
   p.part_ml = reinterpret_cast<float2*>(ws + w.ml_off);
   p.part_o = reinterpret_cast<float*>(ws + w.o_off);
@@ -153,7 +204,7 @@ extern "C" int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h, 
   int rc = tma ? pa_launch_decode_tma(p, sms, st) : pa_launch_decode_generic(p, cache->dtype, ctas, st);
   if (rc) return rc;
   if (pe) cudaEventRecord(pe[1], st);
-  rc = pa_launch_reduce(p, cache->dtype, st);
+  if (!tma) rc = pa_launch_reduce(p, cache->dtype, st);      // the TMA kernel merges its own partials
   if (pe) cudaEventRecord(pe[2], st);
   return rc;
 }
@@ -198,7 +249,7 @@ constexpr int kPrefillChunk = 4096;     // query tokens per decode launch (< PA_
 extern "C" size_t pa_prefill_workspace_bytes(int32_t num_tokens, int32_t num_q_heads, int32_t num_kv_heads,
                                              int32_t head_dim) {
   const int chunk = num_tokens < kPrefillChunk ? (num_tokens > 0 ? num_tokens : 1) : kPrefillChunk;
-  return align_up((size_t)chunk * 4, 256) + pa_decode_workspace_bytes(chunk, num_q_heads, num_kv_heads, head_dim);
+  return pa_decode_workspace_bytes(chunk, num_q_heads, num_kv_heads, head_dim) + align_up((size_t)chunk * 4, 256);
 }
 
 extern "C" int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t o_stride_t,
@@ -213,9 +264,10 @@ extern "C" int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
     return PA_ERR_WORKSPACE;
   const int es = cache->dtype == PA_F32 ? 4 : 2;
   const int chunk_cap = num_tokens < kPrefillChunk ? num_tokens : kPrefillChunk;
-  const size_t lens_bytes = align_up((size_t)chunk_cap * 4, 256);
-  int32_t* lens = static_cast<int32_t*>(workspace);
-  uint8_t* dws = static_cast<uint8_t*>(workspace) + lens_bytes;
+  // the decode workspace (with its zeroed counter header) sits at offset 0; the lens array follows it
+  const size_t dws_bytes = pa_decode_workspace_bytes(chunk_cap, num_q_heads, cache->num_kv_heads, cache->head_dim);
+  uint8_t* dws = static_cast<uint8_t*>(workspace);
+  int32_t* lens = reinterpret_cast<int32_t*>(dws + dws_bytes);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   for (int t0 = 0; t0 < num_tokens; t0 += kPrefillChunk) {
     const int n = num_tokens - t0 < kPrefillChunk ? num_tokens - t0 : kPrefillChunk;
@@ -223,8 +275,7 @@ extern "C" int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
     if (cudaGetLastError() != cudaSuccess) return PA_ERR_CUDA;
     const int rc = pa_decode(static_cast<const uint8_t*>(q) + (int64_t)t0 * q_stride_t * es, q_stride_t, q_stride_h,
                              static_cast<uint8_t*>(out) + (int64_t)t0 * o_stride_t * es, o_stride_t, o_stride_h,
-                             cache, block_table, /*bt_stride=*/0, lens, n, num_q_heads, dws,
-                             workspace_bytes - lens_bytes, stream);
+                             cache, block_table, /*bt_stride=*/0, lens, n, num_q_heads, dws, dws_bytes, stream);
     if (rc) return rc;
   }
   return PA_OK;

@@ -44,7 +44,12 @@ struct PaDecodeParams {
   // workspace
   float* part_o;          // [slots][tile_q][D]
   float2* part_ml;        // [slots][tile_q]  (m in log2 domain, l)
-  int32_t* plan;          // [0] = Q, [1] = total linear blocks, [2 .. 2 + B] = cum[0..B]
+  int32_t* plan;          // [0] = Q, [1] = total linear blocks, [2 .. 2 + B] = cum[0..B]  (generic path)
+  int32_t* counters;      // zero-initialised counter header, left zero by every launch (TMA path)
+  int32_t nc_max;         // upper bound on pool chunks (sizes the partial slots)
+  int32_t pool_div;       // pool = 1 / pool_div of the blocks (0: static split only)
+  int32_t chunk_min;      // smallest pool chunk in blocks
+  long long* dbg;         // optional per-worker timestamps (pa_decode_debug_times), else null
 };
 
 struct PaCursor {
@@ -137,4 +142,7 @@ int pa_launch_decode_generic(const PaDecodeParams& p, int dtype, int ctas, cudaS
 int pa_launch_reduce(const PaDecodeParams& p, int dtype, cudaStream_t stream);
 bool pa_decode_tma_supported(const PaDecodeParams& p, int dtype);
 int pa_decode_tma_workers(int num_sms);
+int pa_decode_tma_nc_max(int num_sms);
+int pa_decode_tma_group();
+int pa_decode_tma_header_ints();
 int pa_decode_generic_workers(int num_sms, int* ctas);

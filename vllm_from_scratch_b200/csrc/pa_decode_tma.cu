@@ -91,6 +91,168 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 __device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
 
+// ------------------------------------------------------------------------------------
+// launch plan (uniform, recomputed by every thread from the block prefix sums)
+// ------------------------------------------------------------------------------------
+// The flattened (sequence, KV head, block) space [0, total) is split in two regions:
+//   static  [0, S)      : worker w owns [w * per_s, (w + 1) * per_s) - one long contiguous range,
+//                         so it leaves at most one partial per segment it touches;
+//   pool    [S, total)  : cut into NC chunks of CH blocks that the workers claim through an atomic
+//                         counter once their static range is done.  SMs do not all get the same
+//                         share of the memory system (ncu: per-SM active cycles spread 75 % .. 95 % of
+//                         the kernel with a purely static split); the pool lets the fast ones absorb
+//                         the difference so that every SM streams until the end.
+// Partials of pool chunks are merged in two levels (groups of kGroup consecutive chunks, then the
+// segment) so that no merge reads more than a few dozen partials.
+struct Plan {
+  int total, per_s, S, CH, NC;
+};
+
+constexpr int kGroup = 32;          // pool chunks per first-level merge group
+constexpr int kChunkMin = 4;        // smallest pool chunk, in blocks (32 KiB of K+V at D = 128)
+constexpr int kPoolDiv = 4;         // pool = 1 / kPoolDiv of the work
+constexpr int kHeaderInts = 16;     // counter header: [0] pool ticket, [1] exited workers
+
+__device__ __forceinline__ Plan make_plan(int total, int W, int nc_max, int pool_div, int chunk_min) {
+  Plan pl;
+  pl.total = total;
+  if (pool_div > 0 && total >= W * 16) {
+    pl.per_s = (total - total / pool_div) / W;
+    pl.S = pl.per_s * W;
+  } else {
+    pl.per_s = max(pa_ceil_div(total, W), PA_MIN_BLOCKS_PER_WORKER);
+    pl.S = total;
+  }
+  const int pool = total - pl.S;
+  pl.CH = max(chunk_min, pa_ceil_div(pool, nc_max));
+  pl.NC = pa_ceil_div(pool, pl.CH);
+  return pl;
+}
+
+// Which ranges touch the segment [a, b) of the linear space.
+struct SegInfo {
+  int w0, ns;        // static workers w0 .. w0 + ns - 1
+  int c0, c1;        // pool chunks c0 .. c1 (valid when ng > 0)
+  int g0, ng;        // chunk groups g0 .. g0 + ng - 1
+  int expected;      // arrivals at the segment counter = ns + ng
+};
+
+__device__ __forceinline__ SegInfo seg_info(const Plan& pl, int a, int b) {
+  SegInfo si;
+  si.w0 = 0; si.ns = 0; si.c0 = 0; si.c1 = -1; si.g0 = 0; si.ng = 0;
+  if (a < pl.S) {
+    si.w0 = a / pl.per_s;
+    si.ns = (min(b, pl.S) - 1) / pl.per_s - si.w0 + 1;
+  }
+  if (b > pl.S) {
+    si.c0 = (max(a, pl.S) - pl.S) / pl.CH;
+    si.c1 = (b - 1 - pl.S) / pl.CH;
+    si.g0 = si.c0 / kGroup;
+    si.ng = si.c1 / kGroup - si.g0 + 1;
+  }
+  si.expected = si.ns + si.ng;
+  return si;
+}
+
+__device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+
+// Merge the partials in slots [lo1, lo1 + n1) and [lo2, lo2 + n2) of one segment (every row of the
+// GQA group) with the usual log-sum-exp weights.  Either normalises and writes out[s, head, :], or
+// writes the merged (unnormalised) partial into `dst_slot`.  Called by a whole warp; lanes own 4
+// consecutive head_dim columns.  Partials were written by other SMs: read them through L2 (ld.cg).
+template <int HD>
+__device__ __noinline__ void merge_partials(const PaDecodeParams& p, int lo1, int n1, int lo2, int n2,
+                                               bool to_out, int dst_slot, int s, int kvh, int lane) {
+  constexpr int RC = 4;                                   // rows merged together
+  constexpr int SU = 8;                                   // sources in flight per round (x RC loads)
+  const int g = p.group, n = n1 + n2;
+  const bool col_ok = lane * 4 < HD;
+  auto slot_of = [&](int i) { return i < n1 ? lo1 + i : lo2 + (i - n1); };
+  for (int r0 = 0; r0 < g; r0 += RC) {
+    // pass 1: running max per row over all sources (lane <-> source)
+    float m[RC];
+#pragma unroll
+    for (int r = 0; r < RC; ++r) m[r] = -INFINITY;
+    for (int i = lane; i < n; i += 32) {
+      const int64_t base = (int64_t)slot_of(i) * g + r0;
+#pragma unroll
+      for (int r = 0; r < RC; ++r)
+        if (r0 + r < g) m[r] = fmaxf(m[r], __ldcg(&p.part_ml[base + r]).x);
+    }
+#pragma unroll
+    for (int r = 0; r < RC; ++r)
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) m[r] = fmaxf(m[r], __shfl_xor_sync(0xffffffffu, m[r], o));
+    float l[RC];
+    float4 acc[RC];
+#pragma unroll
+    for (int r = 0; r < RC; ++r) { l[r] = 0.f; acc[r] = make_float4(0.f, 0.f, 0.f, 0.f); }
+    for (int i0 = 0; i0 < n; i0 += 32) {
+      float w_mine[RC];                                   // lane j: weight of source i0 + j
+#pragma unroll
+      for (int r = 0; r < RC; ++r) w_mine[r] = 0.f;
+      if (i0 + lane < n) {
+        const int64_t base = (int64_t)slot_of(i0 + lane) * g + r0;
+#pragma unroll
+        for (int r = 0; r < RC; ++r)
+          if (r0 + r < g) {
+            const float2 ml = __ldcg(&p.part_ml[base + r]);
+            w_mine[r] = exp2f(ml.x - m[r]);
+            l[r] += ml.y * w_mine[r];
+          }
+      }
+      const int cnt = min(32, n - i0);
+      for (int j0 = 0; j0 < cnt; j0 += SU) {
+        float4 v[SU][RC];
+#pragma unroll
+        for (int u = 0; u < SU; ++u) {
+          const bool live = j0 + u < cnt && col_ok;
+          const int64_t base = live ? ((int64_t)slot_of(i0 + j0 + u) * g + r0) * HD + lane * 4 : 0;
+#pragma unroll
+          for (int r = 0; r < RC; ++r) {
+            v[u][r] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (live && r0 + r < g) v[u][r] = ldcg4(p.part_o + base + r * HD);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < SU; ++u)
+#pragma unroll
+          for (int r = 0; r < RC; ++r) {
+            const float w = __shfl_sync(0xffffffffu, w_mine[r], (j0 + u) & 31);   // 0 past the end
+            acc[r].x = fmaf(w, v[u][r].x, acc[r].x); acc[r].y = fmaf(w, v[u][r].y, acc[r].y);
+            acc[r].z = fmaf(w, v[u][r].z, acc[r].z); acc[r].w = fmaf(w, v[u][r].w, acc[r].w);
+          }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < RC; ++r) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) l[r] += __shfl_xor_sync(0xffffffffu, l[r], o);
+      if (r0 + r >= g) continue;
+      const int row = r0 + r;
+      if (to_out) {
+        const float inv = 1.f / l[r];
+        __nv_bfloat16* op = static_cast<__nv_bfloat16*>(p.out) + (int64_t)s * p.o_stride_b +
+                            (int64_t)(kvh * g + row) * p.o_stride_h + lane * 4;
+        if (col_ok) {
+          if ((reinterpret_cast<uintptr_t>(op) & 7) == 0) {
+            uint2 pk;
+            pk.x = pack_bf16(acc[r].x * inv, acc[r].y * inv);
+            pk.y = pack_bf16(acc[r].z * inv, acc[r].w * inv);
+            *reinterpret_cast<uint2*>(op) = pk;
+          } else {
+            op[0] = __float2bfloat16_rn(acc[r].x * inv); op[1] = __float2bfloat16_rn(acc[r].y * inv);
+            op[2] = __float2bfloat16_rn(acc[r].z * inv); op[3] = __float2bfloat16_rn(acc[r].w * inv);
+          }
+        }
+      } else {
+        if (col_ok) *reinterpret_cast<float4*>(p.part_o + ((int64_t)dst_slot * g + row) * HD + lane * 4) = acc[r];
+        if (lane == 0) p.part_ml[(int64_t)dst_slot * g + row] = make_float2(m[r], l[r]);
+      }
+    }
+  }
+}
+
 // HD: head_dim (64 / 128).  NT: n-tiles of 8 query heads per KV head (g <= 8 * NT).
 template <int HD, int NT>
 __global__ void __launch_bounds__(kWarps * 32, 1)
@@ -101,14 +263,16 @@ pa_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_cons
   constexpr int TILE_BYTES = HALVES * HALF_BYTES;
   constexpr int STAGE_BYTES = 2 * TILE_BYTES; // K tile + V tile
   constexpr int KSTEPS = HD / 16;
+  constexpr uint32_t FULL = 0xffffffffu;
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-  // [kWarps][kStages][STAGE_BYTES] | mbar[kWarps][kStages] (8 B each) | scratch[33] | cum[B + 1]
+  // [kWarps][kStages][STAGE_BYTES] | mbar[kWarps][kStages] | meta[kWarps][kStages] (2 x int4) | scratch[40] | cum[B + 1]
   const uint32_t ring_bytes = kWarps * kStages * STAGE_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_gen + ring_bytes);
-  int* scratch = reinterpret_cast<int*>(bars + kWarps * kStages);
+  int4* meta = reinterpret_cast<int4*>(bars + kWarps * kStages);
+  int* scratch = reinterpret_cast<int*>(meta + 2 * kWarps * kStages);
   int* s_cum = scratch + 40;
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -122,31 +286,75 @@ pa_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_cons
   }
   pa_build_cum(p.seq_lens, p.batch, kBS, s_cum, scratch);   // ends with __syncthreads()
 
+  const int g = p.group;
+  __nv_bfloat16* obase = static_cast<__nv_bfloat16*>(p.out);
+
+  // sequences with no tokens: defined result is zeros (the reference raises, paged_attention.py:93)
+  for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < p.batch; s += gridDim.x * blockDim.x)
+    if (s_cum[s + 1] == s_cum[s])
+      for (int h = 0; h < p.num_q_heads; ++h)
+        for (int d = 0; d < HD; ++d) obase[(int64_t)s * p.o_stride_b + (int64_t)h * p.o_stride_h + d] = __float2bfloat16_rn(0.f);
+
   const int hs = p.num_kv_heads;              // one head segment per KV head (q_tiles == 1)
-  const int total = s_cum[p.batch] * hs;
-  const int per = max(pa_ceil_div(total, p.num_workers), PA_MIN_BLOCKS_PER_WORKER);
-  if (blockIdx.x == 0) {
-    for (int i = threadIdx.x; i <= p.batch; i += blockDim.x) p.plan[2 + i] = s_cum[i];
-    if (threadIdx.x == 0) { p.plan[0] = per; p.plan[1] = total; }
-  }
+  const int W = p.num_workers;
+  const Plan pl = make_plan(s_cum[p.batch] * hs, W, p.nc_max, p.pool_div, p.chunk_min);
+  const int segs = p.batch * hs;
+  const int slot2_base = segs + W + p.nc_max;                    // group partials live after the range partials
+  int* const ticket = p.counters;                                // [0] pool ticket, [1] exited workers
+  int* const grp_cnt = p.counters + kHeaderInts;                 // [seg + group]
+  int* const seg_cnt = grp_cnt + segs + pa_ceil_div(p.nc_max, kGroup);   // [seg]
+
   const int worker = warp * gridDim.x + blockIdx.x;
-  const int lin0 = worker * per;
-  const int count = min(per, total - lin0);
-  if (count <= 0) return;
+  unsigned long long dbg_t0 = 0, dbg_t1 = 0;
+  int dbg_static = 0;
+  if (p.dbg) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(dbg_t0));
+  const uint32_t my_ring = smem_base + warp * (kStages * STAGE_BYTES);
+  const uint32_t my_bars = smem_u32(bars + warp * kStages);
+  int4* my_meta = meta + 2 * warp * kStages;
 
   uint64_t policy;
   asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
 
-  const uint32_t my_ring = smem_base + warp * (kStages * STAGE_BYTES);
-  const uint32_t my_bars = smem_u32(bars + warp * kStages);
+  // ---- producer: walks this worker's ranges (static range, then claimed pool chunks) ----------------
+  int p_uid = worker;                                            // range id: worker, or W + chunk
+  int p_left = min(max(pl.S - worker * pl.per_s, 0), pl.per_s);  // blocks left in the current range
+  bool p_first = true;
+  PaCursor pc;
+  pc.s = pc.h = pc.b = 0; pc.n = 1;
+  if (p_left > 0) pc = pa_locate(s_cum, p.batch, hs, worker * pl.per_s);
+  bool pool_open = pl.NC > 0;
+  int nxt_raw = 0;                                               // lane 0: chunk claimed one range ahead
+  if (pool_open && lane == 0) nxt_raw = atomicAdd(ticket, 1);
+  dbg_static = p_left > 0 ? p_left - 1 : -1;                    // consumer iteration that ends the static range
+  int produced = 0;
+  int bt_reg = 0, bt_s = -1, bt_base = 0;                        // 32 block-table entries cached across the lanes
 
-  PaCursor pc = pa_locate(s_cum, p.batch, hs, lin0);
-  PaCursor cc = pc;
-
-  auto produce = [&](int it) {
+  auto produce = [&]() {
+    if (p_left == 0) {
+      if (!pool_open) return;
+      const int c = __shfl_sync(FULL, nxt_raw, 0);
+      if (c >= pl.NC) { pool_open = false; return; }
+      if (lane == 0) nxt_raw = atomicAdd(ticket, 1);
+      const int lin = pl.S + c * pl.CH;
+      p_uid = W + c;
+      p_left = min(pl.CH, pl.total - lin);
+      pc = pa_locate(s_cum, p.batch, hs, lin);
+      p_first = true;
+    }
+    if (bt_s != pc.s || pc.b < bt_base || pc.b >= bt_base + 32) {
+      bt_s = pc.s;
+      bt_base = pc.b;
+      bt_reg = (bt_base + lane < pc.n) ? __ldg(p.block_tables + (int64_t)pc.s * p.bt_stride + bt_base + lane) : 0;
+    }
+    const int phys = __shfl_sync(FULL, bt_reg, pc.b - bt_base);
+    const bool last_blk = pc.b + 1 == pc.n;
+    const int first = (p_first || pc.b == 0) ? 1 : 0;
+    const int last = (p_left == 1 || last_blk) ? 1 : 0;
     if (lane == 0) {
-      const int stage = it % kStages;
-      const int phys = __ldg(p.block_tables + (int64_t)pc.s * p.bt_stride + pc.b);
+      const int stage = produced % kStages;
+      const int valid = last_blk ? __ldg(p.seq_lens + pc.s) - pc.b * kBS : kBS;
+      my_meta[2 * stage] = make_int4(pc.s, pc.h, pc.b, pc.n);
+      my_meta[2 * stage + 1] = make_int4(p_uid, first | (last << 1), valid, 0);
       const uint32_t bar = my_bars + stage * 8;
       const uint32_t dst = my_ring + stage * STAGE_BYTES;
       const int c1 = p.pos_head == 1 ? pc.h : (p.pos_block == 1 ? phys : 0);
@@ -159,11 +367,14 @@ pa_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_cons
         tma_load_4d(dst + TILE_BYTES + hf * HALF_BYTES, &tm_v, bar, hf * 64, c1, c2, c3, policy);
       }
     }
+    p_first = false;
+    --p_left;
+    ++produced;
     pa_advance(pc, s_cum, p.batch, hs);
   };
 
-  const int prologue = min(kStages, count);
-  for (int it = 0; it < prologue; ++it) produce(it);
+  for (int i = 0; i < kStages; ++i) produce();
+  __syncwarp();
 
   // per-lane constant pieces of the ldmatrix addresses
   const int k_tok = (lane & 7) + ((lane >> 3) & 1) * 8;       // K: matrices 0/1 = tokens 0-7 / 8-15
@@ -174,25 +385,25 @@ pa_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_cons
   const int k_x = k_tok & 7, v_x = v_tok & 7;
 
   const __nv_bfloat16* qbase = static_cast<const __nv_bfloat16*>(p.q);
-  __nv_bfloat16* obase = static_cast<__nv_bfloat16*>(p.out);
-  const int g = p.group;
 
   uint32_t qf[NT][KSTEPS][2];
   float acc[KSTEPS][NT][4];
   float m_run[NT][2], l_run[NT][2];
-  bool seg_start = true;
-  int seg_lin0 = 0;
 
-  for (int it = 0; it < count; ++it) {
+  for (int it = 0; it < produced; ++it) {
     const int stage = it % kStages;
-    if (seg_start) {
-      seg_start = false;
-      seg_lin0 = lin0 + it - cc.b;        // linear index of block 0 of this segment
-      // Q^T B-fragments: b0 = Q[head = lane/4][dim = ks*16 + (lane%4)*2 + {0,1}], b1 = dim + 8
+    mbar_wait(my_bars + stage * 8, (it / kStages) & 1);
+    if (p.dbg && it == dbg_static) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(dbg_t1));
+    const int4 md = my_meta[2 * stage];          // (s, h, b, n)
+    const int4 mf = my_meta[2 * stage + 1];      // (range uid, first | last << 1, valid tokens, -)
+    const int cs = md.x, ch = md.y, cn = md.w;
+
+    if (mf.y & 1) {
+      // new piece: Q^T B-fragments: b0 = Q[head = lane/4][dim = ks*16 + (lane%4)*2 + {0,1}], b1 = dim + 8
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
         const int hq = nt * 8 + (lane >> 2);
-        const __nv_bfloat16* qp = qbase + (int64_t)cc.s * p.q_stride_b + (int64_t)(cc.h * g + hq) * p.q_stride_h +
+        const __nv_bfloat16* qp = qbase + (int64_t)cs * p.q_stride_b + (int64_t)(ch * g + hq) * p.q_stride_h +
                                   (lane & 3) * 2;
 #pragma unroll
         for (int ks = 0; ks < KSTEPS; ++ks) {
@@ -213,7 +424,6 @@ pa_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_cons
         for (int nt = 0; nt < NT; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = acc[mt][nt][2] = acc[mt][nt][3] = 0.f;
     }
 
-    mbar_wait(my_bars + stage * 8, (it / kStages) & 1);
     const uint32_t kt = my_ring + stage * STAGE_BYTES;
     const uint32_t vt = kt + TILE_BYTES;
 
@@ -233,8 +443,7 @@ pa_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_cons
     }
 
     // ---- online softmax over this block's 16 tokens ----------------------------------
-    const int seq_len = __ldg(p.seq_lens + cc.s);
-    const int valid = seq_len - cc.b * kBS;          // >= 1; < 16 only in the last block
+    const int valid = mf.z;                          // >= 1; < 16 only in the last block
     const int t0 = lane >> 2;
     uint32_t pb[NT][2];
     bool need_rescale = false;
@@ -249,9 +458,9 @@ pa_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_cons
         if (t0 >= valid) s0[j] = -INFINITY;
         if (t0 + 8 >= valid) s1[j] = -INFINITY;
         float mx = fmaxf(s0[j], s1[j]);
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+        mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, 4));
+        mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, 8));
+        mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, 16));
         const float m_new = fmaxf(m_run[nt][j], mx);     // finite: token 0 of the block is always valid
         alpha[nt][j] = exp2f(m_run[nt][j] - m_new);      // exp2(-inf) = 0 on the first block
         need_rescale |= (m_new != m_run[nt][j]);
@@ -267,7 +476,7 @@ pa_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_cons
       pb[nt][0] = movm_t(p0);                            // -> B fragment: k = tokens 0-7,  n = head
       pb[nt][1] = movm_t(p1);                            //                k = tokens 8-15
     }
-    if (__any_sync(0xffffffffu, need_rescale)) {
+    if (__any_sync(FULL, need_rescale)) {
 #pragma unroll
       for (int mt = 0; mt < KSTEPS; ++mt)
 #pragma unroll
@@ -301,60 +510,126 @@ pa_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_cons
       for (int nt = 0; nt < NT; ++nt) mma_bf16(acc[mt][nt], a, pb[nt][0], pb[nt][1]);
     }
 
-    // stage consumed by every lane -> refill it
+    // stage (data and meta) consumed by every lane -> refill it
     __syncwarp();
-    if (it + kStages < count) produce(it + kStages);
+    produce();
+    __syncwarp();
 
-    // ---- end of this (sequence, head) segment, or of the worker's range -------------
-    const bool seg_end = (cc.b + 1 == cc.n);
-    if (seg_end || it + 1 == count) {
-      // segment [seg_lin0, seg_lin0 + n) lies inside one worker <=> write the final result
-      const bool whole = (seg_lin0 / per) == ((seg_lin0 + cc.n - 1) / per);
-      const int slot = cc.s * hs + cc.h + worker;
+    if (!(mf.y & 2)) continue;
+
+    // ---- end of a piece = (range, segment) intersection --------------------------------------------
+    float lsum[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        float l = l_run[nt][j];
+        l += __shfl_xor_sync(FULL, l, 4);
+        l += __shfl_xor_sync(FULL, l, 8);
+        l += __shfl_xor_sync(FULL, l, 16);
+        lsum[nt][j] = l;
+      }
+    const int seg = cs * hs + ch;
+    const int lin_a = s_cum[cs] * hs + ch * cn;
+    const SegInfo si = seg_info(pl, lin_a, lin_a + cn);
+    const int uid = mf.x;
+    const bool is_chunk = uid >= W;
+    int gi = 0, cl = 0, eg = 1;                   // this chunk's group, first chunk of (group, segment), arrivals
+    if (is_chunk) {
+      gi = (uid - W) / kGroup;
+      cl = max(gi * kGroup, si.c0);
+      eg = min(gi * kGroup + kGroup - 1, si.c1) - cl + 1;
+    }
+
+    if (si.expected == 1 && eg == 1) {
+      // the whole segment was streamed by this piece: normalise and write the result
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
-        float l[2];
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          l[j] = l_run[nt][j];
-          l[j] += __shfl_xor_sync(0xffffffffu, l[j], 4);
-          l[j] += __shfl_xor_sync(0xffffffffu, l[j], 8);
-          l[j] += __shfl_xor_sync(0xffffffffu, l[j], 16);
-        }
         const int hq = nt * 8 + (lane & 3) * 2;      // this lane's two heads: hq, hq + 1
-        if (whole) {
-          const float inv0 = 1.f / l[0], inv1 = 1.f / l[1];
-          __nv_bfloat16* o0 = obase + (int64_t)cc.s * p.o_stride_b + (int64_t)(cc.h * g + hq) * p.o_stride_h;
-          __nv_bfloat16* o1 = o0 + p.o_stride_h;
+        const float inv0 = 1.f / lsum[nt][0], inv1 = 1.f / lsum[nt][1];
+        __nv_bfloat16* o0 = obase + (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + hq) * p.o_stride_h;
+        __nv_bfloat16* o1 = o0 + p.o_stride_h;
 #pragma unroll
-          for (int mt = 0; mt < KSTEPS; ++mt) {
-            const int d = mt * 16 + (lane >> 2);
-            if (hq < g) {
-              o0[d] = __float2bfloat16_rn(acc[mt][nt][0] * inv0);
-              o0[d + 8] = __float2bfloat16_rn(acc[mt][nt][2] * inv0);
-            }
-            if (hq + 1 < g) {
-              o1[d] = __float2bfloat16_rn(acc[mt][nt][1] * inv1);
-              o1[d + 8] = __float2bfloat16_rn(acc[mt][nt][3] * inv1);
-            }
+        for (int mt = 0; mt < KSTEPS; ++mt) {
+          const int d = mt * 16 + (lane >> 2);
+          if (hq < g) {
+            o0[d] = __float2bfloat16_rn(acc[mt][nt][0] * inv0);
+            o0[d + 8] = __float2bfloat16_rn(acc[mt][nt][2] * inv0);
           }
-        } else {
-          float* po = p.part_o + ((int64_t)slot * p.tile_q + hq) * HD;
-#pragma unroll
-          for (int mt = 0; mt < KSTEPS; ++mt) {
-            const int d = mt * 16 + (lane >> 2);
-            if (hq < g) { po[d] = acc[mt][nt][0]; po[d + 8] = acc[mt][nt][2]; }
-            if (hq + 1 < g) { po[HD + d] = acc[mt][nt][1]; po[HD + d + 8] = acc[mt][nt][3]; }
-          }
-          if ((lane >> 2) == 0) {
-            if (hq < g) p.part_ml[(int64_t)slot * p.tile_q + hq] = make_float2(m_run[nt][0], l[0]);
-            if (hq + 1 < g) p.part_ml[(int64_t)slot * p.tile_q + hq + 1] = make_float2(m_run[nt][1], l[1]);
+          if (hq + 1 < g) {
+            o1[d] = __float2bfloat16_rn(acc[mt][nt][1] * inv1);
+            o1[d + 8] = __float2bfloat16_rn(acc[mt][nt][3] * inv1);
           }
         }
       }
-      seg_start = true;
+      continue;
     }
-    pa_advance(cc, s_cum, p.batch, hs);
+
+    // partial: a lone chunk of its (group, segment) writes straight into the group's slot
+    const bool grp_level = is_chunk && eg > 1;
+    const int slot = (is_chunk && !grp_level) ? slot2_base + seg + gi : seg + uid;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int hq = nt * 8 + (lane & 3) * 2;
+      float* po = p.part_o + ((int64_t)slot * g + hq) * HD;
+#pragma unroll
+      for (int mt = 0; mt < KSTEPS; ++mt) {
+        const int d = mt * 16 + (lane >> 2);
+        if (hq < g) { po[d] = acc[mt][nt][0]; po[d + 8] = acc[mt][nt][2]; }
+        if (hq + 1 < g) { po[HD + d] = acc[mt][nt][1]; po[HD + d + 8] = acc[mt][nt][3]; }
+      }
+      if ((lane >> 2) == 0) {
+        if (hq < g) p.part_ml[(int64_t)slot * g + hq] = make_float2(m_run[nt][0], lsum[nt][0]);
+        if (hq + 1 < g) p.part_ml[(int64_t)slot * g + hq + 1] = make_float2(m_run[nt][1], lsum[nt][1]);
+      }
+    }
+    __threadfence();
+    __syncwarp();
+    bool arrive_seg = !grp_level;
+    if (grp_level) {
+      int old = 0;
+      if (lane == 0) old = atomicAdd(grp_cnt + seg + gi, 1);
+      old = __shfl_sync(FULL, old, 0);
+      if (old == eg - 1) {                           // last chunk of the group in: merge the group
+        if (lane == 0) grp_cnt[seg + gi] = 0;        // self-cleaning: the header stays zero between launches
+        __threadfence();
+        const bool fin = si.expected == 1;
+        merge_partials<HD>(p, seg + W + cl, eg, 0, 0, fin, slot2_base + seg + gi, cs, ch, lane);
+        if (!fin) {
+          __threadfence();
+          __syncwarp();
+          arrive_seg = true;
+        }
+      }
+    }
+    if (arrive_seg) {
+      int old = 0;
+      if (lane == 0) old = atomicAdd(seg_cnt + seg, 1);
+      old = __shfl_sync(FULL, old, 0);
+      if (old == si.expected - 1) {                  // every range of the segment is in: final merge
+        if (lane == 0) seg_cnt[seg] = 0;
+        __threadfence();
+        merge_partials<HD>(p, seg + si.w0, si.ns, slot2_base + seg + si.g0, si.ng, true, 0, cs, ch, lane);
+      }
+    }
+  }
+
+  if (p.dbg && lane == 0) {
+    unsigned long long t2;
+    unsigned smid;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t2));
+    asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+    long long* d = p.dbg + 6 * (int64_t)worker;
+    d[0] = smid; d[1] = (long long)dbg_t0; d[2] = (long long)dbg_t1; d[3] = (long long)t2;
+    d[4] = dbg_static + 1; d[5] = produced;
+  }
+  // ---- exit: the last worker out re-arms the pool ticket for the next launch ----------------------
+  if (lane == 0) {
+    const int nworkers = gridDim.x * kWarps;
+    if (atomicAdd(ticket + 1, 1) == nworkers - 1) {
+      ticket[0] = 0;
+      ticket[1] = 0;
+    }
   }
 }
 
@@ -445,7 +720,7 @@ int get_map(const void* base, const PaDecodeParams& p, CUtensorMap* out, int* po
 template <int HD, int NT>
 int launch(const PaDecodeParams& p, const CUtensorMap& mk, const CUtensorMap& mv, int num_sms, cudaStream_t stream) {
   constexpr int STAGE_BYTES = 2 * (HD / 64) * kBS * 128;
-  const size_t smem = 1024 + (size_t)kWarps * kStages * STAGE_BYTES + kWarps * kStages * 8 + 40 * 4 +
+  const size_t smem = 1024 + (size_t)kWarps * kStages * STAGE_BYTES + kWarps * kStages * (8 + 32) + 40 * 4 +
                       (size_t)(p.batch + 1) * 4 + 16;
   auto kern = pa_decode_tma_kernel<HD, NT>;
   static bool attr_set = false;
@@ -461,6 +736,9 @@ int launch(const PaDecodeParams& p, const CUtensorMap& mk, const CUtensorMap& mv
 }  // namespace
 
 int pa_decode_tma_workers(int num_sms) { return num_sms * kWarps; }
+int pa_decode_tma_nc_max(int num_sms) { return 8 * num_sms * kWarps; }
+int pa_decode_tma_group() { return kGroup; }
+int pa_decode_tma_header_ints() { return kHeaderInts; }
 
 bool pa_decode_tma_supported(const PaDecodeParams& p, int dtype) {
   if (dtype != 0) return false;                                   // bf16 only

@@ -94,12 +94,21 @@ _workspaces = {}
 
 def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
     """Per-device scratch for split-K partials, grown on demand (stream-ordered reuse: callers
-    that launch decode concurrently on several streams must pass their own ``workspace``)."""
+    that launch decode concurrently on several streams must pass their own ``workspace``).
+    Allocated zeroed: the kernels keep the counter header at its start zero between launches."""
     ws = _workspaces.get(device.index)
     if ws is None or ws.numel() < nbytes:
-        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        ws = torch.zeros(max(nbytes, 2 << 20), dtype=torch.uint8, device=device)
         _workspaces[device.index] = ws
     return ws
+
+
+def new_decode_workspace(batch: int, num_q_heads: int, num_kv_heads: int, head_dim: int,
+                         device) -> torch.Tensor:
+    """A private, correctly initialised workspace for ``paged_attention_decode_batched(workspace=...)``
+    (zeroed counter header, include/pa_b200.h)."""
+    return torch.zeros(decode_workspace_bytes(batch, num_q_heads, num_kv_heads, head_dim), dtype=torch.uint8,
+                       device=device)
 
 
 def _as_block_table(block_table, device) -> torch.Tensor:
@@ -247,7 +256,8 @@ def paged_attention_decode_batched(query: torch.Tensor, kv_cache: KvCacheArg, bl
 
     query ``[B, Hq, D]``; block_tables int32 ``[B, max_blocks]`` and seq_lens int32 ``[B]`` on the
     device (no host sync on the launch path); entries past ``ceil(seq_len / BS)`` are never read;
-    ``seq_len == 0`` gives zeros.  Output dtype/device = query's."""
+    ``seq_len == 0`` gives zeros.  Output dtype/device = query's.  A caller-provided ``workspace``
+    must come from ``new_decode_workspace`` (zero-initialised counter header)."""
     desc, kplane = _describe_cache(kv_cache)
     _require_cuda(query, "query")
     _require_cuda(block_tables, "block_tables")
