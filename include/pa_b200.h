@@ -67,8 +67,8 @@ typedef struct PaKvCache {
 /* ---- introspection ------------------------------------------------------ */
 int pa_abi_version(void);
 const char* pa_status_string(int status);
-/* Number of persistent decode workers (warps) the current device runs; the
- * split-K plan and the workspace size depend on it.  <0 on error.           */
+/* Number of persistent decode CTAs the fast path runs on the current device
+ * (one per SM); the workspace size depends on it.  <0 on error.              */
 int pa_decode_num_workers(void);
 
 /* ---- decode (replaces paged_attention_decode, paged_attention.py:67-101,
@@ -79,9 +79,10 @@ int pa_decode_num_workers(void);
  *   never dereferenced.  seq_lens int32 [batch]; seq_len == 0 -> zeros.
  * softmax scale is 1/sqrt(D) (paged_attention.py:80).
  * Split-K ("flash-decoding") over (sequence, KV head, context partition) work
- * ranges, followed by a cross-partition merge.
- * Two launches on the generic path; ONE on the bf16 / block_size 16 fast path,
- * whose kernel merges its own split-K partials ("last arriver merges").
+ * units, followed by a cross-partition merge.
+ * Two launches on the generic path (fp32 caches, odd shapes); ONE on the fast
+ * path (bf16, block_size 16, head_dim 64 / 128, g <= 8), whose kernel merges
+ * its own split-K partials ("the last unit of a segment to arrive merges").
  * workspace: pa_decode_workspace_bytes() bytes, 16-byte aligned, owned by the
  *   caller.  Its first 1 MiB is a counter header that must be ZERO on entry:
  *   call pa_decode_workspace_init once after allocating it (or memset it);
@@ -168,12 +169,15 @@ int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
  * 0 = automatic kernel choice (default); 1 = force the generic CUDA-core
  * decode kernel even for shapes the TMA kernel takes.  Returns the old value. */
 int pa_decode_force_path(int path);
-/* Split-K plan of the fast path: the last 1 / pool_div of the KV blocks is handed out
- * dynamically in chunks of >= chunk_min blocks (pool_div = 0: static split only).      */
-int pa_decode_set_tuning(int pool_div, int chunk_min);
-/* Debug: when non-null, every fast-path worker (warp) writes 6 int64 to
- * device_buffer[6 * worker]: SM id, start / end-of-static-range / end timestamps (ns),
- * blocks in its static range, blocks in total.  pa_decode_num_workers() entries.      */
+/* Split-K granularity of the fast path (guided self-scheduling): a unit handed out when
+ * `remaining` blocks are left is about remaining / (guided_k * SMs) blocks (default 3), never
+ * smaller than total / (units_per_sm * SMs) (1 .. 64, default 16).  stages: per-warp TMA ring
+ * depth, 0 = as deep as shared memory allows.  claim_limit: a CTA claims its next unit
+ * only while fewer than this many claimed KV blocks are unprocessed (default 48).        */
+int pa_decode_set_tuning(int units_per_sm, int guided_k, int stages, int claim_limit);
+/* Debug: when non-null, every fast-path CTA writes 6 int64 to device_buffer[6 * cta]:
+ * SM id, CTA start, consumers' end (globaltimer ns), units processed, finisher's end,
+ * first KV block landed.  pa_decode_num_workers() entries.                              */
 int pa_decode_debug_times(void* device_buffer);
 
 /* ---- per-kernel device timing (bench.py's roofline line) ---------------------

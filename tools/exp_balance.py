@@ -1,4 +1,7 @@
-"""Experiment (not part of the product): split-K plan sweep + per-SM timing of the decode kernel."""
+"""Experiment (not part of the product): units_per_sm sweep + per-CTA timing of the decode kernel.
+
+    python tools/exp_balance.py [c2|c3|c5]
+"""
 import json
 import os
 import sys
@@ -13,7 +16,7 @@ from vllm_from_scratch_b200 import _lib, paged_attention as P  # noqa: E402
 wl_name = sys.argv[1] if len(sys.argv) > 1 else "c2"
 wl = bench.WORKLOADS[wl_name]
 b, ctx, hq, hkv, d, bs, layers, _ = wl
-layers = 4
+layers = min(layers, 4)
 dev = torch.device("cuda", 0)
 lib = _lib.load()
 pool, bts_h, lens_h, q_h, *_ = bench.make_workload(torch, dev, wl, layers, seed=1)
@@ -42,29 +45,39 @@ def timeit(n=300):
 
 run(500)
 res = {}
-settings = [(0, 4), (4, 4), (8, 4), (8, 8), (16, 4), (16, 2), (16, 8), (32, 4), (32, 2), (6, 16), (8, 16)]
-for pd, cm in settings:
-    lib.pa_decode_set_tuning(pd, cm)
+combos = os.environ.get("COMBOS", "24:2:0:48,16:2:0:48,20:2:0:48,28:2:0:48,24:2:0:32,24:2:0:64,24:2:0:96,24:2:0:128,"
+                                  "16:2:0:96,20:2:0:64,24:1:0:48,16:1:0:64,12:2:0:64")
+for combo in combos.split(","):
+    ups, gk, st, cl = (int(x) for x in combo.split(":"))
+    _lib.check(lib.pa_decode_set_tuning(ups, gk, st, cl), "set_tuning")
     us = timeit()
-    res[f"{pd},{cm}"] = us
-    print(f"pool_div={pd:3d} chunk_min={cm:3d}  {us:8.2f} us  {kvb / us / 1e3:8.1f} GB/s", flush=True)
+    res[combo] = us
+    print(f"units_per_sm={ups:3d} guided_k={gk} stages={st} claim={cl:3d}  {us:8.2f} us  {kvb / us / 1e3:8.1f} GB/s",
+          flush=True)
+lib.pa_decode_set_tuning(16, 3, 0, 48)
 
-# per-worker timestamps
+# per-CTA timestamps
 nw = lib.pa_decode_num_workers()
 dbg = torch.zeros(nw * 6, dtype=torch.int64, device=dev)
-allt = {}
-for pd, cm in [(0, 4), (8, 4)]:
-    lib.pa_decode_set_tuning(pd, cm)
-    run(20)
+run(20)
+torch.cuda.synchronize()
+lib.pa_decode_debug_times(dbg.data_ptr())
+recs = []
+for i in range(4):
+    run(1)
     torch.cuda.synchronize()
-    lib.pa_decode_debug_times(dbg.data_ptr())
-    recs = []
-    for i in range(4):
-        run(1)
-        torch.cuda.synchronize()
-        recs.append(dbg.cpu().numpy().reshape(nw, 6).copy())
-    lib.pa_decode_debug_times(None)
-    allt[f"{pd}_{cm}"] = np.stack(recs)
-np.savez(f"gpurun_out/balance_{wl_name}.npz", **allt)
+    recs.append(dbg.cpu().numpy().reshape(nw, 6).copy())
+lib.pa_decode_debug_times(None)
+r = recs[-1]
+t0 = r[:, 1].min()
+end = (r[:, 2] - t0) / 1e3
+fend = (r[:, 4] - t0) / 1e3
+first = (r[:, 5] - t0) / 1e3
+start = (r[:, 1] - t0) / 1e3
+print(f"per-CTA us: start max {start.max():.1f}; first block med {np.median(first):.1f} max {first.max():.1f}; "
+      f"consumers end min {end.min():.1f} med {np.median(end):.1f} max {end.max():.1f}; "
+      f"finisher end med {np.median(fend):.1f} max {fend.max():.1f}; "
+      f"units per CTA min {r[:, 3].min()} max {r[:, 3].max()}", flush=True)
+os.makedirs("gpurun_out", exist_ok=True)
+np.savez(f"gpurun_out/balance_{wl_name}.npz", recs=np.stack(recs))
 json.dump(res, open(f"gpurun_out/balance_{wl_name}.json", "w"))
-lib.pa_decode_set_tuning(4, 4)

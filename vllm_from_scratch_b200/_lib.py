@@ -51,7 +51,7 @@ SIGNATURES = {
     "pa_prefill_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
     "pa_prefill": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
                            c_void_p, c_int32, c_int32, c_int32, c_void_p, c_size_t, c_void_p]),
-    "pa_decode_set_tuning": (c_int, [c_int, c_int]),
+    "pa_decode_set_tuning": (c_int, [c_int, c_int, c_int, c_int]),
     "pa_decode_debug_times": (c_int, [c_void_p]),
     "pa_profile_begin": (c_int, [c_int32]),
     "pa_profile_end": (c_int, [c_void_p, c_void_p, c_int32]),

@@ -13,7 +13,10 @@
 namespace {
 
 std::atomic<int> g_force_path{0};
-std::atomic<int> g_pool_div{4}, g_chunk_min{4};
+std::atomic<int> g_units_per_sm{16};    // fast path: smallest split-K unit = total / (units_per_sm * SMs)
+std::atomic<int> g_guided_k{3};         // fast path: largest unit = remaining / (guided_k * SMs)
+std::atomic<int> g_stages{0};           // fast path: per-warp ring depth override (0 = as deep as fits)
+std::atomic<int> g_claim_limit{48};     // fast path: claim-ahead bound in blocks per CTA
 std::atomic<long long*> g_dbg{nullptr};
 
 int sm_count() {
@@ -56,19 +59,18 @@ struct ProfState {
   bool on = false;
 } g_prof;
 
-// TMA path partial slots: one per (segment, range) + one per (segment, chunk group)
+// The workspace is sized for the largest units_per_sm the tuning hook accepts, so changing the
+// knob never invalidates a workspace the caller already holds.
+constexpr int kMaxUnitsPerSm = 64;
+
+// fast path partial slots: one per work unit
 int64_t tma_slots(int batch, int num_kv_heads, int sms) {
-  const int64_t segs = (int64_t)batch * num_kv_heads;
-  const int nc_max = pa_decode_tma_nc_max(sms);
-  const int ng_max = (nc_max + pa_decode_tma_group() - 1) / pa_decode_tma_group();
-  return 2 * segs + pa_decode_tma_workers(sms) + nc_max + ng_max;
+  return pa_decode_tma_max_units(batch, num_kv_heads, kMaxUnitsPerSm * sms);
 }
 
-bool tma_header_fits(int batch, int num_kv_heads, int sms) {
+bool tma_header_fits(int batch, int num_kv_heads) {
   const int64_t segs = (int64_t)batch * num_kv_heads;
-  const int nc_max = pa_decode_tma_nc_max(sms);
-  const int ng_max = (nc_max + pa_decode_tma_group() - 1) / pa_decode_tma_group();
-  return (size_t)(pa_decode_tma_header_ints() + 2 * segs + ng_max) * 4 <= kHeaderBytes;
+  return (size_t)(pa_decode_tma_header_ints() + segs) * 4 <= kHeaderBytes;
 }
 
 __global__ void pa_iota_lens_kernel(int32_t* lens, int32_t first, int32_t n) {
@@ -95,10 +97,13 @@ extern "C" const char* pa_status_string(int status) {
 
 extern "C" int pa_decode_force_path(int path) { return g_force_path.exchange(path); }
 
-extern "C" int pa_decode_set_tuning(int pool_div, int chunk_min) {
-  if (pool_div < 0 || pool_div == 1 || chunk_min < 1) return PA_ERR_BAD_ARG;
-  g_pool_div.store(pool_div);
-  g_chunk_min.store(chunk_min);
+extern "C" int pa_decode_set_tuning(int units_per_sm, int guided_k, int stages, int claim_limit) {
+  if (units_per_sm < 1 || units_per_sm > kMaxUnitsPerSm || guided_k < 1 || stages < 0 || claim_limit < 1)
+    return PA_ERR_BAD_ARG;
+  g_claim_limit.store(claim_limit);
+  g_units_per_sm.store(units_per_sm);
+  g_guided_k.store(guided_k);
+  g_stages.store(stages);
   return PA_OK;
 }
 
@@ -110,7 +115,7 @@ extern "C" int pa_decode_debug_times(void* device_buffer) {
 extern "C" int pa_decode_num_workers(void) {
   const int sms = sm_count();
   if (sms <= 0) return PA_ERR_NO_DEVICE;
-  return pa_decode_tma_workers(sms);
+  return sms;                                   // one persistent CTA per SM
 }
 
 extern "C" size_t pa_decode_workspace_bytes(int32_t batch, int32_t num_q_heads, int32_t num_kv_heads,
@@ -160,23 +165,23 @@ extern "C" int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h, 
   p.bt_stride = bt_stride;
   p.batch = batch; p.num_q_heads = num_q_heads; p.num_kv_heads = Hkv; p.head_dim = D; p.block_size = BS;
   p.group = num_q_heads / Hkv;
-  p.pos_head = p.pos_block = 0;
+  p.pos_head = 0;
   p.scale_log2e = (float)((1.0 / sqrt((double)D)) * 1.4426950408889634);
 
   const bool tma = g_force_path.load() != 1 && pa_decode_tma_supported(p, cache->dtype) &&
-                   tma_header_fits(batch, Hkv, sms);
+                   tma_header_fits(batch, Hkv);
   int ctas = 0;
   int64_t slots;
   int rows;
-  p.nc_max = 0;
-  p.pool_div = g_pool_div.load();
-  p.chunk_min = g_chunk_min.load();
+  p.num_stages = g_stages.load();
+  p.guided_k = g_guided_k.load();
+  p.claim_limit = g_claim_limit.load();
+  p.target_units = g_units_per_sm.load() * sms;
   p.dbg = g_dbg.load();
   if (tma) {
-    p.tile_q = 8 * ((p.group + 7) / 8);
+    p.tile_q = p.group;
     p.q_tiles = 1;
-    p.num_workers = pa_decode_tma_workers(sms);
-    p.nc_max = pa_decode_tma_nc_max(sms);
+    p.num_workers = sms;
     slots = tma_slots(batch, Hkv, sms);
     rows = p.group;
   } else {

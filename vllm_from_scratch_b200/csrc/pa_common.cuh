@@ -1,6 +1,7 @@
 // Shared device-side definitions for the paged-attention kernels (sm_100a).
 //
-// Work decomposition ("stream-K over KV blocks"):
+// Work decomposition of the GENERIC path ("stream-K over KV blocks"; the bf16 fast path,
+// pa_decode_tma.cu, uses dynamic work units instead and documents its own):
 //   The decode batch is flattened into one linear space of KV blocks,
 //       L = cum[s] * HS + hseg * nblk(s) + b
 //   (s = sequence, hseg = head segment of that sequence, b = logical block,
@@ -39,17 +40,18 @@ struct PaDecodeParams {
   int32_t tile_q;         // q heads per head segment (partial rows per slot)
   int32_t q_tiles;        // ceil(g / tile_q); HS = Hkv * q_tiles
   int32_t num_workers;
-  int32_t pos_head, pos_block;   // TMA coordinate positions (1..3) of the head / block dims
+  int32_t pos_head;       // TMA path: which of tensor-map dims 3 / 4 is the head axis (the other is the block)
+  int32_t num_stages;     // TMA path: ring depth (K + V tile pairs) per CTA
+  int32_t target_units;   // TMA path: split-K work units aimed at per launch (units_per_sm * SMs)
+  int32_t guided_k;       // TMA path: guided self-scheduling divisor (unit ~ remaining / (guided_k * CTAs))
+  int32_t claim_limit;    // TMA path: published-but-unconsumed blocks per CTA above which no new unit is claimed
   float scale_log2e;      // (1 / sqrt(D)) * log2(e)
   // workspace
   float* part_o;          // [slots][tile_q][D]
   float2* part_ml;        // [slots][tile_q]  (m in log2 domain, l)
   int32_t* plan;          // [0] = Q, [1] = total linear blocks, [2 .. 2 + B] = cum[0..B]  (generic path)
   int32_t* counters;      // zero-initialised counter header, left zero by every launch (TMA path)
-  int32_t nc_max;         // upper bound on pool chunks (sizes the partial slots)
-  int32_t pool_div;       // pool = 1 / pool_div of the blocks (0: static split only)
-  int32_t chunk_min;      // smallest pool chunk in blocks
-  long long* dbg;         // optional per-worker timestamps (pa_decode_debug_times), else null
+  long long* dbg;         // optional per-CTA timestamps (pa_decode_debug_times), else null
 };
 
 struct PaCursor {
@@ -141,8 +143,6 @@ int pa_launch_decode_tma(const PaDecodeParams& p, int num_sms, cudaStream_t stre
 int pa_launch_decode_generic(const PaDecodeParams& p, int dtype, int ctas, cudaStream_t stream);
 int pa_launch_reduce(const PaDecodeParams& p, int dtype, cudaStream_t stream);
 bool pa_decode_tma_supported(const PaDecodeParams& p, int dtype);
-int pa_decode_tma_workers(int num_sms);
-int pa_decode_tma_nc_max(int num_sms);
-int pa_decode_tma_group();
 int pa_decode_tma_header_ints();
+int64_t pa_decode_tma_max_units(int batch, int num_kv_heads, int target_units);
 int pa_decode_generic_workers(int num_sms, int* ctas);

@@ -1,28 +1,46 @@
-// Paged-attention decode, bf16, B200 fast path.
+// Paged-attention decode, bf16, B200 fast path (block_size 16, head_dim 64 / 128, g <= 8).
 //
 // Replaces the per-sequence Python loop of the reference
-// (01_paged_attention/paged_attention.py:80-101) for bf16 caches with
-// block_size 16 and head_dim 64 / 128.
+// (01_paged_attention/paged_attention.py:80-101): for every (sequence, KV head) gather the
+// K / V rows through the block table, softmax(q K^T / sqrt(D)) V for the g query heads of the
+// group.  HBM-bound streaming gather at ~4 flop/byte; the design goal is to keep every SM's
+// TMA queue full until the last byte and to read each K / V byte exactly once.
 //
-// Shape of the kernel (HBM-bound streaming gather, ~4 flop/byte):
-//  * persistent grid: one CTA per SM, NWARPS independent warps ("workers") per CTA;
-//    every worker streams an equal, contiguous range of the flattened
-//    (sequence, KV head, block) space (see pa_common.cuh);
-//  * each worker owns a ring of STAGES shared-memory stages; one stage = the K tile
-//    and the V tile of one physical block for one KV head ([16 tokens x D] bf16
-//    each).  Lane 0 looks the physical block up in the block table and issues the
-//    TMA tensor loads (cp.async.bulk.tensor, 128-byte swizzle) that complete on the
-//    stage's mbarrier; the worker refills a stage as soon as it has consumed it, so
-//    NWARPS * STAGES * 8 KiB stay in flight per SM;
-//  * math on legacy tensor cores (mma.sync m16n8k16 bf16, fp32 accumulate) in the
-//    TRANSPOSED formulation so the GQA query heads sit in the n = 8 dimension:
-//        S^T[16 tok x 8 heads] = K[16 x D] . Q^T[D x 8]
-//        O^T[D x 8 heads]     += V^T[D x 16 tok] . P^T[16 tok x 8 heads]
-//    A operands come from shared memory with ldmatrix (K) / ldmatrix.trans (V),
-//    conflict-free under the TMA swizzle; P^T moves from the S^T accumulator layout
-//    to the B-operand layout with movmatrix.  tcgen05 needs M >= 64 and is not a fit
-//    for a 4-row GQA group; the kernel is bound by HBM, not by the tensor pipe;
-//  * online softmax in fp32 (exp2 domain), warp-shuffle reductions over tokens.
+// Shape of the kernel
+//  * split-K "flash-decoding" work units: a (sequence, KV head) segment is cut into units of C
+//    consecutive KV blocks; C (a multiple of 8) is chosen on the device from the batch's total
+//    block count so that there are ~units_per_sm units per SM.  Units are handed out through ONE
+//    atomic ticket in linear (sequence, head, chunk) order.  B200 SMs do not all see the same HBM
+//    bandwidth (the time to stream equal byte counts spreads 75 % .. 100 % across SMs, stable per
+//    SM), so a static split leaves a fifth of the SM-time idle; with the ticket the fast SMs
+//    simply take more units and every SM streams until the end.
+//  * persistent grid, one CTA per SM, 8 consumer warps + a scheduler warp + 4 finisher warps:
+//      scheduler (warp 8): claims tickets one unit ahead, maps ticket -> (s, h, chunk) by binary
+//        search over the per-sequence unit prefix sums in shared memory, reads the unit's block
+//        table entries with coalesced loads and publishes them, a unit descriptor and the unit's
+//        Q rows (cp.async.bulk) into a ring of 8 descriptor slots (full / empty mbarriers).
+//      consumers (warps 0-7): block j of a unit belongs to warp j % 8.  Each warp owns a private
+//        ring of R stages (one stage = K tile + V tile of one block for one KV head, [16 tokens x
+//        D] bf16 each) and is its own TMA producer: a "load cursor" walks the descriptor ring up
+//        to R blocks ahead of the "math cursor", lane 0 issues the two TMA tensor loads of a
+//        block (cp.async.bulk.tensor 5-D, 128-byte swizzle, one instruction per tile) completing
+//        on the stage's mbarrier - 8 independent issuers and R x 8 x 8 KiB in flight per SM, also
+//        while the CTA merges a unit.  Math per block on legacy tensor cores, in the TRANSPOSED
+//        formulation so the GQA query heads sit in the n = 8 dimension:
+//            S^T[16 tok x 8 heads] = K[16 x D] . Q^T[D x 8]          (mma.sync m16n8k16 bf16,
+//            O^T[D x 8 heads]     += V^T[D x 16 tok] . P^T[16 x 8]     fp32 accumulate)
+//        A operands by ldmatrix (K) / ldmatrix.trans (V) straight from the swizzled tiles, P^T from
+//        the S^T accumulator layout to the B layout by movmatrix, fp32 online softmax in the exp2
+//        domain with warp-shuffle reductions.  tcgen05 needs M >= 64 and is not a fit for a <= 8-row
+//        GQA group; the kernel is bound by HBM, not by the tensor pipe.
+//  * at the end of a unit the 8 consumer warps merge their (m, l, O) through shared memory; a
+//    unit that covers its whole segment is normalised and written to `out`, otherwise the merged
+//    partial goes to the workspace (coalesced, 2 KiB at g = 4) and the unit is handed to the
+//    finisher warps, which check it in at the segment's atomic counter; for the last unit of a
+//    segment to arrive they merge the segment's partials and write `out` - no second launch, and
+//    the consumers never wait for a global-memory round trip.
+//  * results are bit-reproducible: the block -> warp assignment and every merge order depend only
+//    on the batch shape, never on which SM took which unit.
 #include <cuda.h>
 #include <mutex>
 #include <string.h>
@@ -31,9 +49,52 @@
 
 namespace {
 
-constexpr int kBS = 16;          // tokens per block on this path
-constexpr int kWarps = 8;        // workers per CTA
-constexpr int kStages = 3;       // ring depth per worker
+constexpr int kBS = 16;             // tokens per block on this path
+constexpr int kConsumers = 8;       // consumer warps per CTA
+constexpr int kFinWarps = 4;        // finisher warps per CTA
+constexpr int kThreads = (kConsumers + 1 + kFinWarps) * 32;   // consumers + scheduler warp + finisher warps
+constexpr int kDescRing = 8;        // unit descriptors in flight scheduler -> consumers
+constexpr int kFinRing = 8;         // finished-unit notices in flight consumers -> finisher
+constexpr int kDescBlocks = 64;     // block-table entries per descriptor (longer units span several)
+constexpr int kMaxStages = 8;       // per-warp ring depth cap
+constexpr int kHeaderInts = 16;     // counter header: [0] unit ticket, [1] exited CTAs, then one int per segment
+constexpr int kMaxBatch = 4096;     // seq_lens + unit prefix sums live in shared memory
+constexpr int kSmemBudget = 227 * 1024;
+constexpr uint32_t FULL = 0xffffffffu;
+
+enum : int { kFirst = 1, kLast = 2 };   // descriptor flags: first / last descriptor of its unit
+
+struct UnitDesc {                   // 32 bytes
+  int s, h;                         // sequence, KV head
+  int n, flags;                     // blocks in this descriptor (0: end of stream), kFirst | kLast
+  int last_valid;                   // valid tokens in the unit's final block
+  int nch;                          // units of this segment
+  int slot, slot0;                  // this unit's ticket (= partial slot), ticket of the segment's first unit
+};
+
+// Shared-memory carve-up, identical on host and device.
+struct SmemLayout {
+  uint32_t ring, merge_o, merge_ml, qring, bt, desc, fin, bars, scratch, lens, cs, ucum, total;
+};
+__host__ __device__ inline SmemLayout smem_layout(int hd, int g, int r, int batch) {
+  SmemLayout L;
+  const uint32_t stage = 2u * (hd / 64) * kBS * 128;
+  uint32_t o = 0;
+  L.ring = o;      o += (uint32_t)kConsumers * r * stage;
+  L.merge_o = o;   o += (uint32_t)kConsumers * g * (hd + 4) * 4;
+  L.merge_ml = o;  o += kConsumers * 8 * 8;
+  L.qring = o;     o += (uint32_t)kDescRing * g * hd * 2;
+  L.bt = o;        o += kDescRing * kDescBlocks * 4;
+  L.desc = o;      o += kDescRing * 32;
+  L.fin = o;       o += 2 * kFinRing * 16 + 16;          // notices, merge jobs, {jobs, end}
+  L.bars = o;      o += (uint32_t)(kConsumers * kMaxStages + 3 * kDescRing + 2 * kFinRing) * 8;
+  L.scratch = o;   o += 48 * 4;
+  L.lens = o;      o += (uint32_t)batch * 4;
+  L.cs = o;        o += (uint32_t)(batch + 1) * 4;
+  L.ucum = o;      o += (uint32_t)(batch + 1) * 4;
+  L.total = o + 1024;               // slack for the 1024-byte alignment of the ring
+  return L;
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -43,6 +104,20 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(done)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return done != 0;
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done;
@@ -56,12 +131,18 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "memory");
   } while (!done);
 }
-__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
-                                            int c0, int c1, int c2, int c3, uint64_t policy) {
+__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                            int c3, int c4, uint64_t policy) {
   asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
-      " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(policy)
+      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %3, %3, %4, %5}], [%2], %6;"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(0), "r"(c3), "r"(c4), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
       : "memory");
 }
 __device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
@@ -90,292 +171,318 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 }
 __device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
-
-// ------------------------------------------------------------------------------------
-// launch plan (uniform, recomputed by every thread from the block prefix sums)
-// ------------------------------------------------------------------------------------
-// The flattened (sequence, KV head, block) space [0, total) is split in two regions:
-//   static  [0, S)      : worker w owns [w * per_s, (w + 1) * per_s) - one long contiguous range,
-//                         so it leaves at most one partial per segment it touches;
-//   pool    [S, total)  : cut into NC chunks of CH blocks that the workers claim through an atomic
-//                         counter once their static range is done.  SMs do not all get the same
-//                         share of the memory system (ncu: per-SM active cycles spread 75 % .. 95 % of
-//                         the kernel with a purely static split); the pool lets the fast ones absorb
-//                         the difference so that every SM streams until the end.
-// Partials of pool chunks are merged in two levels (groups of kGroup consecutive chunks, then the
-// segment) so that no merge reads more than a few dozen partials.
-struct Plan {
-  int total, per_s, S, CH, NC;
-};
-
-constexpr int kGroup = 32;          // pool chunks per first-level merge group
-constexpr int kChunkMin = 4;        // smallest pool chunk, in blocks (32 KiB of K+V at D = 128)
-constexpr int kPoolDiv = 4;         // pool = 1 / kPoolDiv of the work
-constexpr int kHeaderInts = 16;     // counter header: [0] pool ticket, [1] exited workers
-
-__device__ __forceinline__ Plan make_plan(int total, int W, int nc_max, int pool_div, int chunk_min) {
-  Plan pl;
-  pl.total = total;
-  if (pool_div > 0 && total >= W * 16) {
-    pl.per_s = (total - total / pool_div) / W;
-    pl.S = pl.per_s * W;
-  } else {
-    pl.per_s = max(pa_ceil_div(total, W), PA_MIN_BLOCKS_PER_WORKER);
-    pl.S = total;
-  }
-  const int pool = total - pl.S;
-  pl.CH = max(chunk_min, pa_ceil_div(pool, nc_max));
-  pl.NC = pa_ceil_div(pool, pl.CH);
-  return pl;
+__device__ __forceinline__ void consumer_bar() {
+  asm volatile("bar.sync 1, %0;" ::"n"(kConsumers * 32) : "memory");
 }
-
-// Which ranges touch the segment [a, b) of the linear space.
-struct SegInfo {
-  int w0, ns;        // static workers w0 .. w0 + ns - 1
-  int c0, c1;        // pool chunks c0 .. c1 (valid when ng > 0)
-  int g0, ng;        // chunk groups g0 .. g0 + ng - 1
-  int expected;      // arrivals at the segment counter = ns + ng
-};
-
-__device__ __forceinline__ SegInfo seg_info(const Plan& pl, int a, int b) {
-  SegInfo si;
-  si.w0 = 0; si.ns = 0; si.c0 = 0; si.c1 = -1; si.g0 = 0; si.ng = 0;
-  if (a < pl.S) {
-    si.w0 = a / pl.per_s;
-    si.ns = (min(b, pl.S) - 1) / pl.per_s - si.w0 + 1;
-  }
-  if (b > pl.S) {
-    si.c0 = (max(a, pl.S) - pl.S) / pl.CH;
-    si.c1 = (b - 1 - pl.S) / pl.CH;
-    si.g0 = si.c0 / kGroup;
-    si.ng = si.c1 / kGroup - si.g0 + 1;
-  }
-  si.expected = si.ns + si.ng;
-  return si;
-}
-
 __device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
 
-// Merge the partials in slots [lo1, lo1 + n1) and [lo2, lo2 + n2) of one segment (every row of the
-// GQA group) with the usual log-sum-exp weights.  Either normalises and writes out[s, head, :], or
-// writes the merged (unnormalised) partial into `dst_slot`.  Called by a whole warp; lanes own 4
-// consecutive head_dim columns.  Partials were written by other SMs: read them through L2 (ld.cg).
-template <int HD>
-__device__ __noinline__ void merge_partials(const PaDecodeParams& p, int lo1, int n1, int lo2, int n2,
-                                               bool to_out, int dst_slot, int s, int kvh, int lane) {
-  constexpr int RC = 4;                                   // rows merged together
-  constexpr int SU = 8;                                   // sources in flight per round (x RC loads)
-  const int g = p.group, n = n1 + n2;
-  const bool col_ok = lane * 4 < HD;
-  auto slot_of = [&](int i) { return i < n1 ? lo1 + i : lo2 + (i - n1); };
-  for (int r0 = 0; r0 < g; r0 += RC) {
-    // pass 1: running max per row over all sources (lane <-> source)
-    float m[RC];
+// Exclusive scan of a[0 .. n) in place (shared memory), a[n] = total.  Called by ONE warp (the
+// scheduler); lanes own contiguous slices.
+__device__ __forceinline__ int warp_scan_inplace(int* a, int n, int lane) {
+  const int per = pa_ceil_div(n, 32);
+  const int lo = min(lane * per, n), hi = min(lo + per, n);
+  int mine = 0;
+  for (int i = lo; i < hi; ++i) mine += a[i];
+  int incl = mine;
 #pragma unroll
-    for (int r = 0; r < RC; ++r) m[r] = -INFINITY;
-    for (int i = lane; i < n; i += 32) {
-      const int64_t base = (int64_t)slot_of(i) * g + r0;
-#pragma unroll
-      for (int r = 0; r < RC; ++r)
-        if (r0 + r < g) m[r] = fmaxf(m[r], __ldcg(&p.part_ml[base + r]).x);
-    }
-#pragma unroll
-    for (int r = 0; r < RC; ++r)
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) m[r] = fmaxf(m[r], __shfl_xor_sync(0xffffffffu, m[r], o));
-    float l[RC];
-    float4 acc[RC];
-#pragma unroll
-    for (int r = 0; r < RC; ++r) { l[r] = 0.f; acc[r] = make_float4(0.f, 0.f, 0.f, 0.f); }
-    for (int i0 = 0; i0 < n; i0 += 32) {
-      float w_mine[RC];                                   // lane j: weight of source i0 + j
-#pragma unroll
-      for (int r = 0; r < RC; ++r) w_mine[r] = 0.f;
-      if (i0 + lane < n) {
-        const int64_t base = (int64_t)slot_of(i0 + lane) * g + r0;
-#pragma unroll
-        for (int r = 0; r < RC; ++r)
-          if (r0 + r < g) {
-            const float2 ml = __ldcg(&p.part_ml[base + r]);
-            w_mine[r] = exp2f(ml.x - m[r]);
-            l[r] += ml.y * w_mine[r];
-          }
-      }
-      const int cnt = min(32, n - i0);
-      for (int j0 = 0; j0 < cnt; j0 += SU) {
-        float4 v[SU][RC];
-#pragma unroll
-        for (int u = 0; u < SU; ++u) {
-          const bool live = j0 + u < cnt && col_ok;
-          const int64_t base = live ? ((int64_t)slot_of(i0 + j0 + u) * g + r0) * HD + lane * 4 : 0;
-#pragma unroll
-          for (int r = 0; r < RC; ++r) {
-            v[u][r] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (live && r0 + r < g) v[u][r] = ldcg4(p.part_o + base + r * HD);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < SU; ++u)
-#pragma unroll
-          for (int r = 0; r < RC; ++r) {
-            const float w = __shfl_sync(0xffffffffu, w_mine[r], (j0 + u) & 31);   // 0 past the end
-            acc[r].x = fmaf(w, v[u][r].x, acc[r].x); acc[r].y = fmaf(w, v[u][r].y, acc[r].y);
-            acc[r].z = fmaf(w, v[u][r].z, acc[r].z); acc[r].w = fmaf(w, v[u][r].w, acc[r].w);
-          }
-      }
-    }
-#pragma unroll
-    for (int r = 0; r < RC; ++r) {
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) l[r] += __shfl_xor_sync(0xffffffffu, l[r], o);
-      if (r0 + r >= g) continue;
-      const int row = r0 + r;
-      if (to_out) {
-        const float inv = 1.f / l[r];
-        __nv_bfloat16* op = static_cast<__nv_bfloat16*>(p.out) + (int64_t)s * p.o_stride_b +
-                            (int64_t)(kvh * g + row) * p.o_stride_h + lane * 4;
-        if (col_ok) {
-          if ((reinterpret_cast<uintptr_t>(op) & 7) == 0) {
-            uint2 pk;
-            pk.x = pack_bf16(acc[r].x * inv, acc[r].y * inv);
-            pk.y = pack_bf16(acc[r].z * inv, acc[r].w * inv);
-            *reinterpret_cast<uint2*>(op) = pk;
-          } else {
-            op[0] = __float2bfloat16_rn(acc[r].x * inv); op[1] = __float2bfloat16_rn(acc[r].y * inv);
-            op[2] = __float2bfloat16_rn(acc[r].z * inv); op[3] = __float2bfloat16_rn(acc[r].w * inv);
-          }
-        }
-      } else {
-        if (col_ok) *reinterpret_cast<float4*>(p.part_o + ((int64_t)dst_slot * g + row) * HD + lane * 4) = acc[r];
-        if (lane == 0) p.part_ml[(int64_t)dst_slot * g + row] = make_float2(m[r], l[r]);
-      }
-    }
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(FULL, incl, o);
+    if (lane >= o) incl += t;
   }
+  const int total = __shfl_sync(FULL, incl, 31);
+  int run = incl - mine;
+  for (int i = lo; i < hi; ++i) {
+    const int v = a[i];
+    a[i] = run;
+    run += v;
+  }
+  if (lane == 0) a[n] = total;
+  __syncwarp();
+  return total;
 }
 
-// HD: head_dim (64 / 128).  NT: n-tiles of 8 query heads per KV head (g <= 8 * NT).
-template <int HD, int NT>
-__global__ void __launch_bounds__(kWarps * 32, 1)
-pa_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
-                     const PaDecodeParams p) {
+// Launch plan, built by the scheduler warp of every CTA (nobody else needs it, so the consumers
+// are already waiting for their first descriptor meanwhile).  Blocks per unit are chosen PER
+// SEQUENCE by guided self-scheduling: C(s) ~ (blocks from sequence s to the end) / (guided_k *
+// CTAs), so the units handed out first are large (few partials, few merges; whole segments while
+// they are short enough) and the last ones small (every SM streams until the end), never below
+// the uniform size that yields target_units units.  C(s) is a multiple of 8: every consumer warp
+// gets the same share of a full unit.  Outputs: s_len[s] = max(seq_len, 0), s_c[s] = C(s),
+// s_ucum = exclusive scan of ceil(nblk(s) / C(s)) (s_ucum[batch] = units per KV head).
+__device__ __forceinline__ void build_plan(const int32_t* __restrict__ seq_lens, int batch, int hs, int target_units,
+                                           int guided_div, int* s_len, int* s_c, int* s_ucum, int lane) {
+  for (int i = lane; i < batch; i += 32) {
+    const int len = max(__ldg(seq_lens + i), 0);
+    s_len[i] = len;
+    s_c[i] = pa_ceil_div(len, kBS);
+  }
+  __syncwarp();
+  const int total = warp_scan_inplace(s_c, batch, lane) * hs;             // s_c[s] = blocks before sequence s
+  const int c_min = 8 * max(1, pa_ceil_div(total, 8 * target_units));
+  for (int i = lane; i < batch; i += 32) {
+    const int nblk = pa_ceil_div(s_len[i], kBS);
+    const int remaining = total - s_c[i] * hs;
+    int c = max(c_min, 8 * (remaining / (8 * guided_div)));
+    c = min(c, 8 * pa_ceil_div(max(nblk, 1), 8));
+    s_ucum[i] = pa_ceil_div(nblk, c);
+    s_c[i] = c;                     // only this lane touches s_c[i] in this loop
+  }
+  __syncwarp();
+  warp_scan_inplace(s_ucum, batch, lane);
+}
+
+template <int HD>
+__global__ void __launch_bounds__(kThreads, 1)
+pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
+                    const PaDecodeParams p) {
   constexpr int HALVES = HD / 64;             // 128-byte column halves of a row
   constexpr int HALF_BYTES = kBS * 128;       // one [16 x 64] bf16 box
   constexpr int TILE_BYTES = HALVES * HALF_BYTES;
   constexpr int STAGE_BYTES = 2 * TILE_BYTES; // K tile + V tile
   constexpr int KSTEPS = HD / 16;
-  constexpr uint32_t FULL = 0xffffffffu;
+  constexpr int OPITCH = HD + 4;              // merge row pitch in floats (bank-conflict-free writes)
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-  // [kWarps][kStages][STAGE_BYTES] | mbar[kWarps][kStages] | meta[kWarps][kStages] (2 x int4) | scratch[40] | cum[B + 1]
-  const uint32_t ring_bytes = kWarps * kStages * STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_gen + ring_bytes);
-  int4* meta = reinterpret_cast<int4*>(bars + kWarps * kStages);
-  int* scratch = reinterpret_cast<int*>(meta + 2 * kWarps * kStages);
-  int* s_cum = scratch + 40;
+  const int g = p.group, R = p.num_stages;
+  const SmemLayout L = smem_layout(HD, g, R, p.batch);
+  float* merge_o = reinterpret_cast<float*>(smem_gen + L.merge_o);
+  float2* merge_ml = reinterpret_cast<float2*>(smem_gen + L.merge_ml);
+  int* bt_ring = reinterpret_cast<int*>(smem_gen + L.bt);
+  UnitDesc* desc = reinterpret_cast<UnitDesc*>(smem_gen + L.desc);
+  int4* fin = reinterpret_cast<int4*>(smem_gen + L.fin);               // (segment, nch, slot0, -)
+  int* scratch = reinterpret_cast<int*>(smem_gen + L.scratch);
+  int* s_len = reinterpret_cast<int*>(smem_gen + L.lens);
+  int* s_c = reinterpret_cast<int*>(smem_gen + L.cs);
+  int* s_ucum = reinterpret_cast<int*>(smem_gen + L.ucum);
+  const uint32_t qring = smem_base + L.qring;
+  const uint32_t bar_full = smem_base + L.bars;                          // [kConsumers][kMaxStages]
+  const uint32_t bar_dfull = bar_full + kConsumers * kMaxStages * 8;     // [kDescRing]
+  const uint32_t bar_dempty = bar_dfull + kDescRing * 8;                 // [kDescRing]
+  const uint32_t bar_qfull = bar_dempty + kDescRing * 8;                 // [kDescRing]
+  const uint32_t bar_ffull = bar_qfull + kDescRing * 8;                  // [kFinRing]
+  const uint32_t bar_fempty = bar_ffull + kFinRing * 8;                  // [kFinRing]
+  const uint32_t q_bytes = (uint32_t)g * HD * 2;
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
+  unsigned long long dbg_t0 = 0;
+  if (p.dbg && threadIdx.x == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(dbg_t0));
+
   if (threadIdx.x == 0) {
-#pragma unroll
-    for (int i = 0; i < kWarps * kStages; ++i) mbar_init(smem_u32(bars + i), 1);
+    for (int i = 0; i < kConsumers * kMaxStages; ++i) mbar_init(bar_full + i * 8, 1);
+    for (int i = 0; i < kDescRing; ++i) {
+      mbar_init(bar_dfull + i * 8, 1);
+      mbar_init(bar_dempty + i * 8, kConsumers);
+      mbar_init(bar_qfull + i * 8, 1);
+    }
+    for (int i = 0; i < kFinRing; ++i) {
+      mbar_init(bar_ffull + i * 8, 1);
+      mbar_init(bar_fempty + i * 8, 1);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_k) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_v) : "memory");
   }
-  pa_build_cum(p.seq_lens, p.batch, kBS, s_cum, scratch);   // ends with __syncthreads()
+  const int hs = p.num_kv_heads;
+  int* const ticket = p.counters;                            // [0] unit ticket, [1] exited CTAs
+  int* const seg_cnt = p.counters + kHeaderInts;             // [segment]
+  // The first ticket is requested before the plan is built: its latency hides behind the plan.
+  int tk = 0;
+  if (warp == kConsumers && lane == 0) tk = atomicAdd(ticket, 1);
 
-  const int g = p.group;
+  __syncthreads();                                           // mbarriers are initialised
   __nv_bfloat16* obase = static_cast<__nv_bfloat16*>(p.out);
 
-  // sequences with no tokens: defined result is zeros (the reference raises, paged_attention.py:93)
-  for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < p.batch; s += gridDim.x * blockDim.x)
-    if (s_cum[s + 1] == s_cum[s])
-      for (int h = 0; h < p.num_q_heads; ++h)
-        for (int d = 0; d < HD; ++d) obase[(int64_t)s * p.o_stride_b + (int64_t)h * p.o_stride_h + d] = __float2bfloat16_rn(0.f);
-
-  const int hs = p.num_kv_heads;              // one head segment per KV head (q_tiles == 1)
-  const int W = p.num_workers;
-  const Plan pl = make_plan(s_cum[p.batch] * hs, W, p.nc_max, p.pool_div, p.chunk_min);
-  const int segs = p.batch * hs;
-  const int slot2_base = segs + W + p.nc_max;                    // group partials live after the range partials
-  int* const ticket = p.counters;                                // [0] pool ticket, [1] exited workers
-  int* const grp_cnt = p.counters + kHeaderInts;                 // [seg + group]
-  int* const seg_cnt = grp_cnt + segs + pa_ceil_div(p.nc_max, kGroup);   // [seg]
-
-  const int worker = warp * gridDim.x + blockIdx.x;
-  unsigned long long dbg_t0 = 0, dbg_t1 = 0;
-  int dbg_static = 0;
-  if (p.dbg) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(dbg_t0));
-  const uint32_t my_ring = smem_base + warp * (kStages * STAGE_BYTES);
-  const uint32_t my_bars = smem_u32(bars + warp * kStages);
-  int4* my_meta = meta + 2 * warp * kStages;
-
-  uint64_t policy;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
-
-  // ---- producer: walks this worker's ranges (static range, then claimed pool chunks) ----------------
-  int p_uid = worker;                                            // range id: worker, or W + chunk
-  int p_left = min(max(pl.S - worker * pl.per_s, 0), pl.per_s);  // blocks left in the current range
-  bool p_first = true;
-  PaCursor pc;
-  pc.s = pc.h = pc.b = 0; pc.n = 1;
-  if (p_left > 0) pc = pa_locate(s_cum, p.batch, hs, worker * pl.per_s);
-  bool pool_open = pl.NC > 0;
-  int nxt_raw = 0;                                               // lane 0: chunk claimed one range ahead
-  if (pool_open && lane == 0) nxt_raw = atomicAdd(ticket, 1);
-  dbg_static = p_left > 0 ? p_left - 1 : -1;                    // consumer iteration that ends the static range
-  int produced = 0;
-  int bt_reg = 0, bt_s = -1, bt_base = 0;                        // 32 block-table entries cached across the lanes
-
-  auto produce = [&]() {
-    if (p_left == 0) {
-      if (!pool_open) return;
-      const int c = __shfl_sync(FULL, nxt_raw, 0);
-      if (c >= pl.NC) { pool_open = false; return; }
-      if (lane == 0) nxt_raw = atomicAdd(ticket, 1);
-      const int lin = pl.S + c * pl.CH;
-      p_uid = W + c;
-      p_left = min(pl.CH, pl.total - lin);
-      pc = pa_locate(s_cum, p.batch, hs, lin);
-      p_first = true;
+  if (warp == kConsumers) {
+    // =========================== scheduler warp ==========================================
+    build_plan(p.seq_lens, p.batch, hs, p.target_units, p.guided_k * (int)gridDim.x, s_len, s_c, s_ucum, lane);
+    const int NU = s_ucum[p.batch] * hs;
+    // sequences with no tokens: defined result is zeros (the reference raises, paged_attention.py:93)
+    for (int s = blockIdx.x; s < p.batch; s += gridDim.x)
+      if (s_len[s] == 0)
+        for (int e = lane; e < p.num_q_heads * HD; e += 32)
+          obase[(int64_t)s * p.o_stride_b + (int64_t)(e / HD) * p.o_stride_h + e % HD] = __float2bfloat16_rn(0.f);
+    const __nv_bfloat16* qbase = static_cast<const __nv_bfloat16*>(p.q);
+    // One unit of look-ahead: `nx_*` is claimed, located and has its first 64 block-table entries
+    // in flight while the current unit is being published.
+    int nx_s = 0, nx_h = 0, nx_b0 = 0, nx_n = 0, nx_nch = 0, nx_t = 0, nx_c = 0, nx_bt0 = 0, nx_bt1 = 0;
+    auto setup_next = [&]() {
+      nx_t = __shfl_sync(FULL, tk, 0);
+      if (nx_t >= NU) { nx_n = 0; return; }
+      if (lane == 0) tk = atomicAdd(ticket, 1);
+      const PaCursor cu = pa_locate(s_ucum, p.batch, hs, nx_t);     // (s, h, chunk, chunks)
+      nx_s = cu.s; nx_h = cu.h; nx_c = cu.b; nx_nch = cu.n;
+      const int C = s_c[cu.s];
+      nx_b0 = cu.b * C;
+      nx_n = min(C, pa_ceil_div(s_len[cu.s], kBS) - nx_b0);
+      const int32_t* row = p.block_tables + (int64_t)cu.s * p.bt_stride + nx_b0;
+      nx_bt0 = lane < nx_n ? __ldg(row + lane) : 0;
+      nx_bt1 = lane + 32 < nx_n ? __ldg(row + lane + 32) : 0;
+    };
+    int u = 0;                                                       // descriptors published so far
+    // Claim-ahead is bounded in BLOCKS: a unit is published (and the next ticket claimed) only when
+    // fewer than `claim_limit` published blocks are still unconsumed - enough to cover the ticket and
+    // block-table round trips, small enough that no CTA hoards work the others could be doing.
+    int rel = 0, outstanding = 0;                                    // descriptors [rel, u) not known released
+    int* const hist = scratch;                                       // blocks of descriptor slot i
+    auto wait_release = [&]() {
+      if (lane == 0) mbar_wait(bar_dempty + (rel % kDescRing) * 8, (rel / kDescRing) & 1);
+      __syncwarp();
+      outstanding -= hist[rel % kDescRing];
+      ++rel;
+    };
+    setup_next();
+    while (nx_n > 0) {
+      const int cs = nx_s, ch = nx_h, b0 = nx_b0, n = nx_n, nch = nx_nch, t = nx_t, c = nx_c;
+      int bt0 = nx_bt0, bt1 = nx_bt1;
+      while (rel < u && outstanding + min(n, kDescBlocks) > p.claim_limit) wait_release();
+      const int len = s_len[cs];
+      const int last_valid = (b0 + n == pa_ceil_div(len, kBS)) ? len - (b0 + n - 1) * kBS : kBS;
+      for (int j0 = 0; j0 < n; j0 += kDescBlocks) {
+        const int nd = min(kDescBlocks, n - j0);
+        if (j0 > 0) {
+          const int32_t* row = p.block_tables + (int64_t)cs * p.bt_stride + b0 + j0;
+          bt0 = lane < nd ? __ldg(row + lane) : 0;
+          bt1 = lane + 32 < nd ? __ldg(row + lane + 32) : 0;
+        }
+        const int ds = u % kDescRing;
+        while (u - rel >= kDescRing) wait_release();                 // the slot's previous occupant is released
+        hist[ds] = nd;
+        outstanding += nd;
+        bt_ring[ds * kDescBlocks + lane] = bt0;
+        bt_ring[ds * kDescBlocks + lane + 32] = bt1;
+        __syncwarp();
+        if (lane == 0) {
+          UnitDesc d;
+          d.s = cs; d.h = ch; d.n = nd;
+          d.flags = (j0 == 0 ? kFirst : 0) | (j0 + nd == n ? kLast : 0);
+          d.last_valid = last_valid; d.nch = nch; d.slot = t; d.slot0 = t - c;
+          desc[ds] = d;
+          mbar_arrive(bar_dfull + ds * 8);                           // the consumers may start loading K / V
+          if (j0 == 0) {                                             // Q rides its own barrier: needed at math time only
+            mbar_expect_tx(bar_qfull + ds * 8, q_bytes);
+            bulk_load(qring + ds * q_bytes, qbase + (int64_t)cs * p.q_stride_b + (int64_t)(ch * g) * p.q_stride_h,
+                      q_bytes, bar_qfull + ds * 8);
+          } else {
+            mbar_arrive(bar_qfull + ds * 8);
+          }
+        }
+        ++u;
+      }
+      setup_next();
     }
-    if (bt_s != pc.s || pc.b < bt_base || pc.b >= bt_base + 32) {
-      bt_s = pc.s;
-      bt_base = pc.b;
-      bt_reg = (bt_base + lane < pc.n) ? __ldg(p.block_tables + (int64_t)pc.s * p.bt_stride + bt_base + lane) : 0;
-    }
-    const int phys = __shfl_sync(FULL, bt_reg, pc.b - bt_base);
-    const bool last_blk = pc.b + 1 == pc.n;
-    const int first = (p_first || pc.b == 0) ? 1 : 0;
-    const int last = (p_left == 1 || last_blk) ? 1 : 0;
+    while (u - rel >= kDescRing) wait_release();
     if (lane == 0) {
-      const int stage = produced % kStages;
-      const int valid = last_blk ? __ldg(p.seq_lens + pc.s) - pc.b * kBS : kBS;
-      my_meta[2 * stage] = make_int4(pc.s, pc.h, pc.b, pc.n);
-      my_meta[2 * stage + 1] = make_int4(p_uid, first | (last << 1), valid, 0);
-      const uint32_t bar = my_bars + stage * 8;
-      const uint32_t dst = my_ring + stage * STAGE_BYTES;
-      const int c1 = p.pos_head == 1 ? pc.h : (p.pos_block == 1 ? phys : 0);
-      const int c2 = p.pos_head == 2 ? pc.h : (p.pos_block == 2 ? phys : 0);
-      const int c3 = p.pos_head == 3 ? pc.h : (p.pos_block == 3 ? phys : 0);
-      mbar_expect_tx(bar, STAGE_BYTES);
-#pragma unroll
-      for (int hf = 0; hf < HALVES; ++hf) {
-        tma_load_4d(dst + hf * HALF_BYTES, &tm_k, bar, hf * 64, c1, c2, c3, policy);
-        tma_load_4d(dst + TILE_BYTES + hf * HALF_BYTES, &tm_v, bar, hf * 64, c1, c2, c3, policy);
+      const int ds = u % kDescRing;
+      desc[ds].n = 0;                                   // end of stream
+      mbar_arrive(bar_dfull + ds * 8);
+      // the last CTA out re-arms the ticket for the next launch (the header stays zero between launches)
+      if (atomicAdd(ticket + 1, 1) == (int)gridDim.x - 1) {
+        ticket[0] = 0;
+        ticket[1] = 0;
       }
     }
-    p_first = false;
-    --p_left;
-    ++produced;
-    pa_advance(pc, s_cum, p.batch, hs);
-  };
+    return;
+  }
 
-  for (int i = 0; i < kStages; ++i) produce();
-  __syncwarp();
+  if (warp > kConsumers) {
+    // =========================== finisher warps ==========================================
+    // The leader (first finisher warp) checks finished units in at their segment's counter; for
+    // the last unit of a segment to arrive the four warps merge the segment's partials (one row of
+    // the GQA group per warp) and write `out`.  Every global round trip costs microseconds while
+    // the SMs saturate HBM (tens of MB are queued ahead of it), so notices are taken in batches -
+    // lane i owns notice i, ONE fence and ONE atomic round trip serve the batch - and a merge has
+    // 16 partials' loads in flight per lane.  The consumers never wait for any of this.
+    const int fw = warp - kConsumers - 1;
+    int4* const jobs = fin + kFinRing;                          // (segment, nch, slot0, -)
+    int* const ctl = reinterpret_cast<int*>(fin + 2 * kFinRing);   // [0] jobs in this batch, [1] end of stream
+    int k = 0;
+    for (;;) {
+      if (fw == 0) {
+        int4 e = make_int4(0, 0, 0, 0);
+        int m = 0, end = 0;                                     // notices in this batch
+        for (; m < kFinRing; ++m) {
+          const int f = (k + m) % kFinRing;
+          const uint32_t par = ((k + m) / kFinRing) & 1;
+          if (m == 0) mbar_wait(bar_ffull + f * 8, par);
+          else if (!mbar_test(bar_ffull + f * 8, par)) break;
+          const int4 t = fin[f];
+          if (lane == m) e = t;
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_fempty + f * 8);
+          if (t.y == 0) { end = 1; ++m; break; }
+        }
+        k += m;
+        int last = 0;
+        if (lane < m && e.y > 0) {
+          __threadfence();                // cumulative: the CTA's partial writes (ordered by the notice) before the count
+          last = atomicAdd(seg_cnt + e.x, 1) == e.y - 1;
+          if (last) seg_cnt[e.x] = 0;     // self-cleaning: the header stays zero between launches
+        }
+        const unsigned todo = __ballot_sync(FULL, last);
+        if (last) jobs[__popc(todo & ((1u << lane) - 1))] = e;
+        if (lane == 0) { ctl[0] = __popc(todo); ctl[1] = end; }
+        if (todo) __threadfence();        // partials were written by other SMs: read them through L2
+      }
+      asm volatile("bar.sync 2, %0;" ::"n"(kFinWarps * 32) : "memory");
+      const int njobs = ctl[0], end = ctl[1];
+      for (int j = 0; j < njobs; ++j) {
+        const int4 e = jobs[j];
+        const int seg = e.x, nch = e.y, slot0 = e.z;
+        const int cs = seg / hs, ch = seg - cs * hs;
+        for (int row = fw; row < g; row += kFinWarps) {
+          for (int dq = lane * 4; dq < HD; dq += 128) {
+            float M = -INFINITY, Ls = 0.f;
+            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int k0 = 0; k0 < nch; k0 += 16) {
+              float2 ml[16];
+              float4 v[16];
+#pragma unroll
+              for (int kk = 0; kk < 16; ++kk) {
+                const bool live = k0 + kk < nch;
+                const int64_t r = live ? (int64_t)(slot0 + k0 + kk) * g + row : 0;
+                ml[kk] = live ? __ldcg(p.part_ml + r) : make_float2(-INFINITY, 0.f);
+                v[kk] = live ? ldcg4(p.part_o + r * HD + dq) : make_float4(0.f, 0.f, 0.f, 0.f);
+              }
+#pragma unroll
+              for (int kk = 0; kk < 16; ++kk) {
+                const float Mn = fmaxf(M, ml[kk].x);
+                // a live partial has a finite max (every unit holds >= 1 valid token); dead entries weigh 0
+                const float a = Mn == -INFINITY ? 0.f : exp2f(M - Mn);
+                const float b = Mn == -INFINITY ? 0.f : exp2f(ml[kk].x - Mn);
+                Ls = Ls * a + ml[kk].y * b;
+                o.x = o.x * a + v[kk].x * b; o.y = o.y * a + v[kk].y * b;
+                o.z = o.z * a + v[kk].z * b; o.w = o.w * a + v[kk].w * b;
+                M = Mn;
+              }
+            }
+            const float inv = 1.f / Ls;
+            __nv_bfloat16* op = obase + (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + row) * p.o_stride_h + dq;
+            reinterpret_cast<uint32_t*>(op)[0] = pack_bf16(o.x * inv, o.y * inv);
+            reinterpret_cast<uint32_t*>(op)[1] = pack_bf16(o.z * inv, o.w * inv);
+          }
+        }
+      }
+      asm volatile("bar.sync 2, %0;" ::"n"(kFinWarps * 32) : "memory");     // jobs consumed: the leader may refill
+      if (end) break;
+    }
+    if (p.dbg && fw == 0 && lane == 0) {
+      unsigned long long t1;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+      p.dbg[6 * (int64_t)blockIdx.x + 4] = (long long)t1;
+    }
+    return;
+  }
 
+  // ============================= consumer warps ============================================
+  const int ctid = threadIdx.x;                               // 0 .. 255
+  uint64_t policy;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  const bool head3 = p.pos_head == 3;                         // which of tensor-map dims 3 / 4 is the head axis
+  const uint32_t my_ring = smem_base + L.ring + warp * (R * STAGE_BYTES);
+  const uint32_t my_full = bar_full + warp * (kMaxStages * 8);
   // per-lane constant pieces of the ldmatrix addresses
   const int k_tok = (lane & 7) + ((lane >> 3) & 1) * 8;       // K: matrices 0/1 = tokens 0-7 / 8-15
   const int k_csel = lane >> 4;                               //    matrices 2/3 = next 8 dims
@@ -383,253 +490,260 @@ pa_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_cons
   const int v_csel = (lane >> 3) & 1;                         //      matrices 1/3 = next 8 dims
   const uint32_t k_row = k_tok * 128, v_row = v_tok * 128;
   const int k_x = k_tok & 7, v_x = v_tok & 7;
+  const int hq_b = lane >> 2;                                 // query head of this lane's B-fragment column
+  const int hq_c = (lane & 3) * 2;                            // first of this lane's two accumulator heads
+  float* my_mo = merge_o + warp * g * OPITCH;
 
-  const __nv_bfloat16* qbase = static_cast<const __nv_bfloat16*>(p.q);
+  // ---- load cursor: walks this warp's blocks (j = warp, warp + 8, ... of every descriptor) up to R
+  //      blocks ahead of the math cursor and issues their TMA loads ---------------------------------
+  int pu = 0, pj = warp;            // descriptor index, block index within it
+  int p_known = -1;                 // descriptors up to here are known to be published
+  bool p_end = false;
+  int produced = 0, consumed = 0;   // this warp's blocks: loads issued / blocks processed
+  int p_stage = 0, c_stage = 0, c_phase = 0;
+  auto try_produce = [&](bool blocking) -> bool {
+    int ds;
+    for (;;) {
+      if (p_end) return false;
+      ds = pu % kDescRing;
+      if (pu > p_known) {
+        const uint32_t par = (pu / kDescRing) & 1;
+        if (blocking) mbar_wait(bar_dfull + ds * 8, par);
+        else if (!mbar_test(bar_dfull + ds * 8, par)) return false;
+        p_known = pu;
+      }
+      const int n = desc[ds].n;
+      if (n == 0) { p_end = true; return false; }
+      if (pj < n) break;
+      ++pu;                                             // no (more) blocks of this warp in that descriptor
+      pj = warp;
+    }
+    const int phys = bt_ring[ds * kDescBlocks + pj];
+    const int ph = desc[ds].h;
+    if (lane == 0) {
+      const uint32_t bar = my_full + p_stage * 8;
+      const uint32_t dst = my_ring + p_stage * STAGE_BYTES;
+      const int c3 = head3 ? ph : phys, c4 = head3 ? phys : ph;
+      mbar_expect_tx(bar, STAGE_BYTES);
+      tma_load_5d(dst, &tm_k, bar, c3, c4, policy);
+      tma_load_5d(dst + TILE_BYTES, &tm_v, bar, c3, c4, policy);
+    }
+    pj += kConsumers;
+    ++produced;
+    if (++p_stage == R) p_stage = 0;
+    return true;
+  };
 
-  uint32_t qf[NT][KSTEPS][2];
-  float acc[KSTEPS][NT][4];
-  float m_run[NT][2], l_run[NT][2];
+  uint32_t qf[KSTEPS][2];
+  float acc[KSTEPS][4];
+  float m_run[2], l_run[2];
+  int units_done = 0, fin_count = 0;
+  unsigned long long dbg_first = 0;       // when this CTA's first KV block had landed
 
-  for (int it = 0; it < produced; ++it) {
-    const int stage = it % kStages;
-    mbar_wait(my_bars + stage * 8, (it / kStages) & 1);
-    if (p.dbg && it == dbg_static) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(dbg_t1));
-    const int4 md = my_meta[2 * stage];          // (s, h, b, n)
-    const int4 mf = my_meta[2 * stage + 1];      // (range uid, first | last << 1, valid tokens, -)
-    const int cs = md.x, ch = md.y, cn = md.w;
+  for (int cu = 0;; ++cu) {
+    const int ds = cu % kDescRing;
+    mbar_wait(bar_dfull + ds * 8, (cu / kDescRing) & 1);
+    if (cu > p_known) p_known = cu;
+    const int4 d0 = reinterpret_cast<const int4*>(desc + ds)[0];      // s, h, n, flags
+    const int4 d1 = reinterpret_cast<const int4*>(desc + ds)[1];      // last_valid, nch, slot, slot0
+    if (d0.z == 0) break;
+    const int cs = d0.x, ch = d0.y, n = d0.z, flags = d0.w;
+    const int last_valid = d1.x, nch = d1.y, slot = d1.z, slot0 = d1.w;
 
-    if (mf.y & 1) {
-      // new piece: Q^T B-fragments: b0 = Q[head = lane/4][dim = ks*16 + (lane%4)*2 + {0,1}], b1 = dim + 8
+    while (produced - consumed < R && try_produce(false)) {}            // get K / V moving before waiting for Q
+    if (flags & kFirst) {
+      mbar_wait(bar_qfull + ds * 8, (cu / kDescRing) & 1);
+      // Q^T B-fragments: b0 = Q[head = lane/4][dim = ks*16 + (lane%4)*2 + {0,1}], b1 = dim + 8
+      const uint32_t qs = qring + ds * q_bytes + hq_b * (HD * 2) + (lane & 3) * 4;
 #pragma unroll
-      for (int nt = 0; nt < NT; ++nt) {
-        const int hq = nt * 8 + (lane >> 2);
-        const __nv_bfloat16* qp = qbase + (int64_t)cs * p.q_stride_b + (int64_t)(ch * g + hq) * p.q_stride_h +
-                                  (lane & 3) * 2;
-#pragma unroll
-        for (int ks = 0; ks < KSTEPS; ++ks) {
-          uint32_t b0 = 0, b1 = 0;
-          if (hq < g) {
-            b0 = __ldg(reinterpret_cast<const uint32_t*>(qp + ks * 16));
-            b1 = __ldg(reinterpret_cast<const uint32_t*>(qp + ks * 16 + 8));
-          }
-          qf[nt][ks][0] = b0;
-          qf[nt][ks][1] = b1;
+      for (int ks = 0; ks < KSTEPS; ++ks) {
+        uint32_t b0 = 0, b1 = 0;
+        if (hq_b < g) {
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(b0) : "r"(qs + ks * 32));
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(b1) : "r"(qs + ks * 32 + 16));
         }
-        m_run[nt][0] = m_run[nt][1] = -INFINITY;
-        l_run[nt][0] = l_run[nt][1] = 0.f;
+        qf[ks][0] = b0;
+        qf[ks][1] = b1;
       }
+      m_run[0] = m_run[1] = -INFINITY;
+      l_run[0] = l_run[1] = 0.f;
 #pragma unroll
-      for (int mt = 0; mt < KSTEPS; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) acc[mt][nt][0] = acc[mt][nt][1] = acc[mt][nt][2] = acc[mt][nt][3] = 0.f;
+      for (int mt = 0; mt < KSTEPS; ++mt) acc[mt][0] = acc[mt][1] = acc[mt][2] = acc[mt][3] = 0.f;
     }
 
-    const uint32_t kt = my_ring + stage * STAGE_BYTES;
-    const uint32_t vt = kt + TILE_BYTES;
-
-    // ---- S^T = K . Q^T ----------------------------------------------------------
-    float sc[NT][2][4];
-#pragma unroll
-    for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-      for (int c = 0; c < 2; ++c) sc[nt][c][0] = sc[nt][c][1] = sc[nt][c][2] = sc[nt][c][3] = 0.f;
-#pragma unroll
-    for (int ks = 0; ks < KSTEPS; ++ks) {
-      uint32_t a[4];
-      const int chunk = (ks & 3) * 2 + k_csel;
-      ldsm_x4(a, kt + (ks >> 2) * HALF_BYTES + k_row + ((chunk ^ k_x) << 4));
-#pragma unroll
-      for (int nt = 0; nt < NT; ++nt) mma_bf16(sc[nt][ks & 1], a, qf[nt][ks][0], qf[nt][ks][1]);
-    }
-
-    // ---- online softmax over this block's 16 tokens ----------------------------------
-    const int valid = mf.z;                          // >= 1; < 16 only in the last block
-    const int t0 = lane >> 2;
-    uint32_t pb[NT][2];
-    bool need_rescale = false;
-    float alpha[NT][2];
-#pragma unroll
-    for (int nt = 0; nt < NT; ++nt) {
-      float s0[2], s1[2];
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        s0[j] = (sc[nt][0][j] + sc[nt][1][j]) * p.scale_log2e;           // token t0,     head 2*(lane%4)+j
-        s1[j] = (sc[nt][0][j + 2] + sc[nt][1][j + 2]) * p.scale_log2e;   // token t0 + 8
-        if (t0 >= valid) s0[j] = -INFINITY;
-        if (t0 + 8 >= valid) s1[j] = -INFINITY;
-        float mx = fmaxf(s0[j], s1[j]);
-        mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, 4));
-        mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, 8));
-        mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, 16));
-        const float m_new = fmaxf(m_run[nt][j], mx);     // finite: token 0 of the block is always valid
-        alpha[nt][j] = exp2f(m_run[nt][j] - m_new);      // exp2(-inf) = 0 on the first block
-        need_rescale |= (m_new != m_run[nt][j]);
-        m_run[nt][j] = m_new;
-        s0[j] = exp2f(s0[j] - m_new);
-        s1[j] = exp2f(s1[j] - m_new);
-      }
-      const uint32_t p0 = pack_bf16(s0[0], s0[1]);       // token t0:     heads (2c, 2c+1)
-      const uint32_t p1 = pack_bf16(s1[0], s1[1]);       // token t0 + 8
-      // the normaliser sums the SAME bf16-rounded weights the PV product uses
-      l_run[nt][0] = l_run[nt][0] * alpha[nt][0] + bf16lo(p0) + bf16lo(p1);
-      l_run[nt][1] = l_run[nt][1] * alpha[nt][1] + bf16hi(p0) + bf16hi(p1);
-      pb[nt][0] = movm_t(p0);                            // -> B fragment: k = tokens 0-7,  n = head
-      pb[nt][1] = movm_t(p1);                            //                k = tokens 8-15
-    }
-    if (__any_sync(FULL, need_rescale)) {
-#pragma unroll
-      for (int mt = 0; mt < KSTEPS; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-          acc[mt][nt][0] *= alpha[nt][0];
-          acc[mt][nt][1] *= alpha[nt][1];
-          acc[mt][nt][2] *= alpha[nt][0];
-          acc[mt][nt][3] *= alpha[nt][1];
-        }
-    }
-
-    // A V row of a token past seq_len may hold anything (Inf/NaN bit patterns in a recycled
-    // block); 0 * NaN would poison the product, so clear those rows in shared memory.
-    if (valid < kBS) {
-      for (int i = lane; i < (kBS - valid) * (HD / 8); i += 32) {
-        const int row = valid + i / (HD / 8), c = i % (HD / 8);
-        const uint32_t a = vt + (c >> 3) * HALF_BYTES + row * 128 + (((c & 7) ^ (row & 7)) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(a), "r"(0) : "memory");
-      }
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    for (int cj = warp; cj < n; cj += kConsumers) {
+      while (produced - consumed < R && try_produce(false)) {}
+      if (produced == consumed) try_produce(true);       // the load cursor is exactly here: cannot block
       __syncwarp();
-    }
+      mbar_wait(my_full + c_stage * 8, c_phase);
+      if (p.dbg && threadIdx.x == 0 && dbg_first == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(dbg_first));
+      const uint32_t kt = my_ring + c_stage * STAGE_BYTES;
+      const uint32_t vt = kt + TILE_BYTES;
 
-    // ---- O^T += V^T . P^T -------------------------------------------------------
+      // ---- S^T = K . Q^T ----------------------------------------------------------
+      float sc[2][4];
 #pragma unroll
-    for (int mt = 0; mt < KSTEPS; ++mt) {
-      uint32_t a[4];
-      const int chunk = (mt & 3) * 2 + v_csel;
-      ldsm_x4_t(a, vt + (mt >> 2) * HALF_BYTES + v_row + ((chunk ^ v_x) << 4));
+      for (int c = 0; c < 2; ++c) sc[c][0] = sc[c][1] = sc[c][2] = sc[c][3] = 0.f;
 #pragma unroll
-      for (int nt = 0; nt < NT; ++nt) mma_bf16(acc[mt][nt], a, pb[nt][0], pb[nt][1]);
-    }
-
-    // stage (data and meta) consumed by every lane -> refill it
-    __syncwarp();
-    produce();
-    __syncwarp();
-
-    if (!(mf.y & 2)) continue;
-
-    // ---- end of a piece = (range, segment) intersection --------------------------------------------
-    float lsum[NT][2];
-#pragma unroll
-    for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        float l = l_run[nt][j];
-        l += __shfl_xor_sync(FULL, l, 4);
-        l += __shfl_xor_sync(FULL, l, 8);
-        l += __shfl_xor_sync(FULL, l, 16);
-        lsum[nt][j] = l;
+      for (int ks = 0; ks < KSTEPS; ++ks) {
+        uint32_t a[4];
+        const int chunk = (ks & 3) * 2 + k_csel;
+        ldsm_x4(a, kt + (ks >> 2) * HALF_BYTES + k_row + ((chunk ^ k_x) << 4));
+        mma_bf16(sc[ks & 1], a, qf[ks][0], qf[ks][1]);
       }
-    const int seg = cs * hs + ch;
-    const int lin_a = s_cum[cs] * hs + ch * cn;
-    const SegInfo si = seg_info(pl, lin_a, lin_a + cn);
-    const int uid = mf.x;
-    const bool is_chunk = uid >= W;
-    int gi = 0, cl = 0, eg = 1;                   // this chunk's group, first chunk of (group, segment), arrivals
-    if (is_chunk) {
-      gi = (uid - W) / kGroup;
-      cl = max(gi * kGroup, si.c0);
-      eg = min(gi * kGroup + kGroup - 1, si.c1) - cl + 1;
-    }
 
-    if (si.expected == 1 && eg == 1) {
-      // the whole segment was streamed by this piece: normalise and write the result
+      // ---- online softmax over this block's 16 tokens ----------------------------------
+      const int valid = ((flags & kLast) && cj == n - 1) ? last_valid : kBS;   // < 16 only in a sequence's last block
+      const int t0 = lane >> 2;
+      uint32_t pb[2];
+      bool need_rescale = false;
+      float alpha[2];
+      {
+        float s0[2], s1[2];
 #pragma unroll
-      for (int nt = 0; nt < NT; ++nt) {
-        const int hq = nt * 8 + (lane & 3) * 2;      // this lane's two heads: hq, hq + 1
-        const float inv0 = 1.f / lsum[nt][0], inv1 = 1.f / lsum[nt][1];
-        __nv_bfloat16* o0 = obase + (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + hq) * p.o_stride_h;
-        __nv_bfloat16* o1 = o0 + p.o_stride_h;
+        for (int j = 0; j < 2; ++j) {
+          s0[j] = (sc[0][j] + sc[1][j]) * p.scale_log2e;           // token t0,     head hq_c + j
+          s1[j] = (sc[0][j + 2] + sc[1][j + 2]) * p.scale_log2e;   // token t0 + 8
+          if (t0 >= valid) s0[j] = -INFINITY;
+          if (t0 + 8 >= valid) s1[j] = -INFINITY;
+          float mx = fmaxf(s0[j], s1[j]);
+          mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, 4));
+          mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, 8));
+          mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, 16));
+          const float m_new = fmaxf(m_run[j], mx);       // finite: token 0 of the block is always valid
+          alpha[j] = exp2f(m_run[j] - m_new);            // exp2(-inf) = 0 on the first block
+          need_rescale |= (m_new != m_run[j]);
+          m_run[j] = m_new;
+          s0[j] = exp2f(s0[j] - m_new);
+          s1[j] = exp2f(s1[j] - m_new);
+        }
+        const uint32_t p0 = pack_bf16(s0[0], s0[1]);       // token t0:     heads (hq_c, hq_c + 1)
+        const uint32_t p1 = pack_bf16(s1[0], s1[1]);       // token t0 + 8
+        // the normaliser sums the SAME bf16-rounded weights the PV product uses
+        l_run[0] = l_run[0] * alpha[0] + bf16lo(p0) + bf16lo(p1);
+        l_run[1] = l_run[1] * alpha[1] + bf16hi(p0) + bf16hi(p1);
+        pb[0] = movm_t(p0);                                // -> B fragment: k = tokens 0-7,  n = head
+        pb[1] = movm_t(p1);                                //                k = tokens 8-15
+      }
+      if (__any_sync(FULL, need_rescale)) {
 #pragma unroll
         for (int mt = 0; mt < KSTEPS; ++mt) {
-          const int d = mt * 16 + (lane >> 2);
-          if (hq < g) {
-            o0[d] = __float2bfloat16_rn(acc[mt][nt][0] * inv0);
-            o0[d + 8] = __float2bfloat16_rn(acc[mt][nt][2] * inv0);
-          }
-          if (hq + 1 < g) {
-            o1[d] = __float2bfloat16_rn(acc[mt][nt][1] * inv1);
-            o1[d + 8] = __float2bfloat16_rn(acc[mt][nt][3] * inv1);
-          }
+          acc[mt][0] *= alpha[0];
+          acc[mt][1] *= alpha[1];
+          acc[mt][2] *= alpha[0];
+          acc[mt][3] *= alpha[1];
         }
       }
-      continue;
-    }
 
-    // partial: a lone chunk of its (group, segment) writes straight into the group's slot
-    const bool grp_level = is_chunk && eg > 1;
-    const int slot = (is_chunk && !grp_level) ? slot2_base + seg + gi : seg + uid;
+      // A V row of a token past seq_len may hold anything (Inf/NaN bit patterns in a recycled
+      // block); 0 * NaN would poison the product, so clear those rows in shared memory.
+      if (valid < kBS) {
+        for (int e = lane; e < (kBS - valid) * (HD / 8); e += 32) {
+          const int row = valid + e / (HD / 8), c = e % (HD / 8);
+          const uint32_t a = vt + (c >> 3) * HALF_BYTES + row * 128 + (((c & 7) ^ (row & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(a), "r"(0) : "memory");
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+      }
+
+      // ---- O^T += V^T . P^T -------------------------------------------------------
 #pragma unroll
-    for (int nt = 0; nt < NT; ++nt) {
-      const int hq = nt * 8 + (lane & 3) * 2;
-      float* po = p.part_o + ((int64_t)slot * g + hq) * HD;
+      for (int mt = 0; mt < KSTEPS; ++mt) {
+        uint32_t a[4];
+        const int chunk = (mt & 3) * 2 + v_csel;
+        ldsm_x4_t(a, vt + (mt >> 2) * HALF_BYTES + v_row + ((chunk ^ v_x) << 4));
+        mma_bf16(acc[mt], a, pb[0], pb[1]);
+      }
+
+      // stage consumed by every lane -> it may be refilled
+      __syncwarp();
+      ++consumed;
+      if (++c_stage == R) { c_stage = 0; c_phase ^= 1; }
+    }
+    // keep the ring full across the merge below, then hand the descriptor slot back
+    if (pu == cu) { pu = cu + 1; pj = warp; }             // the load cursor never reads a released slot
+    while (produced - consumed < R && try_produce(false)) {}
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_dempty + ds * 8);
+    if (!(flags & kLast)) continue;
+
+    // ---- end of the unit: merge the 8 warps' (m, l, O) through shared memory ---------------------
+    float lsum[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      float l = l_run[j];
+      l += __shfl_xor_sync(FULL, l, 4);
+      l += __shfl_xor_sync(FULL, l, 8);
+      l += __shfl_xor_sync(FULL, l, 16);
+      lsum[j] = l;
+    }
+    if (m_run[0] != -INFINITY) {          // warp-uniform: this warp had at least one block of the unit
 #pragma unroll
       for (int mt = 0; mt < KSTEPS; ++mt) {
         const int d = mt * 16 + (lane >> 2);
-        if (hq < g) { po[d] = acc[mt][nt][0]; po[d + 8] = acc[mt][nt][2]; }
-        if (hq + 1 < g) { po[HD + d] = acc[mt][nt][1]; po[HD + d + 8] = acc[mt][nt][3]; }
-      }
-      if ((lane >> 2) == 0) {
-        if (hq < g) p.part_ml[(int64_t)slot * g + hq] = make_float2(m_run[nt][0], lsum[nt][0]);
-        if (hq + 1 < g) p.part_ml[(int64_t)slot * g + hq + 1] = make_float2(m_run[nt][1], lsum[nt][1]);
+        if (hq_c < g) { my_mo[hq_c * OPITCH + d] = acc[mt][0]; my_mo[hq_c * OPITCH + d + 8] = acc[mt][2]; }
+        if (hq_c + 1 < g) { my_mo[(hq_c + 1) * OPITCH + d] = acc[mt][1]; my_mo[(hq_c + 1) * OPITCH + d + 8] = acc[mt][3]; }
       }
     }
-    __threadfence();
-    __syncwarp();
-    bool arrive_seg = !grp_level;
-    if (grp_level) {
-      int old = 0;
-      if (lane == 0) old = atomicAdd(grp_cnt + seg + gi, 1);
-      old = __shfl_sync(FULL, old, 0);
-      if (old == eg - 1) {                           // last chunk of the group in: merge the group
-        if (lane == 0) grp_cnt[seg + gi] = 0;        // self-cleaning: the header stays zero between launches
-        __threadfence();
-        const bool fin = si.expected == 1;
-        merge_partials<HD>(p, seg + W + cl, eg, 0, 0, fin, slot2_base + seg + gi, cs, ch, lane);
-        if (!fin) {
-          __threadfence();
-          __syncwarp();
-          arrive_seg = true;
+    if ((lane >> 2) == 0) {
+      if (hq_c < g) merge_ml[warp * 8 + hq_c] = make_float2(m_run[0], lsum[0]);
+      if (hq_c + 1 < g) merge_ml[warp * 8 + hq_c + 1] = make_float2(m_run[1], lsum[1]);
+    }
+    consumer_bar();                                            // A: every warp's state is in shared memory
+
+    for (int e2 = ctid; e2 < g * (HD / 2); e2 += kConsumers * 32) {
+      const int head = e2 / (HD / 2), dp = (e2 - head * (HD / 2)) * 2;
+      float M = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < kConsumers; ++w) M = fmaxf(M, merge_ml[w * 8 + head].x);
+      float Lsum = 0.f, o0 = 0.f, o1 = 0.f;
+#pragma unroll
+      for (int w = 0; w < kConsumers; ++w) {
+        const float2 ml = merge_ml[w * 8 + head];
+        if (ml.x != -INFINITY) {
+          const float wg = exp2f(ml.x - M);
+          const float2 v = *reinterpret_cast<const float2*>(merge_o + (w * g + head) * OPITCH + dp);
+          Lsum = fmaf(ml.y, wg, Lsum);
+          o0 = fmaf(v.x, wg, o0);
+          o1 = fmaf(v.y, wg, o1);
         }
       }
-    }
-    if (arrive_seg) {
-      int old = 0;
-      if (lane == 0) old = atomicAdd(seg_cnt + seg, 1);
-      old = __shfl_sync(FULL, old, 0);
-      if (old == si.expected - 1) {                  // every range of the segment is in: final merge
-        if (lane == 0) seg_cnt[seg] = 0;
-        __threadfence();
-        merge_partials<HD>(p, seg + si.w0, si.ns, slot2_base + seg + si.g0, si.ng, true, 0, cs, ch, lane);
+      if (nch == 1) {
+        const float inv = 1.f / Lsum;
+        *reinterpret_cast<uint32_t*>(obase + (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + head) * p.o_stride_h + dp) =
+            pack_bf16(o0 * inv, o1 * inv);
+      } else {
+        *reinterpret_cast<float2*>(p.part_o + ((int64_t)slot * g + head) * HD + dp) = make_float2(o0, o1);
+        if (dp == 0) p.part_ml[(int64_t)slot * g + head] = make_float2(M, Lsum);
       }
     }
+    consumer_bar();                       // B: merge_* are free again; the partial is complete CTA-wide
+    ++units_done;
+
+    if (nch > 1 && ctid == 0) {
+      // hand the finished unit to the finisher warp (notice ring; blocks only if it is 8 units behind)
+      const int f = fin_count % kFinRing;
+      mbar_wait(bar_fempty + f * 8, ((fin_count / kFinRing) & 1) ^ 1);
+      fin[f] = make_int4(cs * hs + ch, nch, slot0, 0);
+      mbar_arrive(bar_ffull + f * 8);
+    }
+    if (nch > 1) ++fin_count;
+  }
+  if (ctid == 0) {                        // end of stream for the finisher
+    const int f = fin_count % kFinRing;
+    mbar_wait(bar_fempty + f * 8, ((fin_count / kFinRing) & 1) ^ 1);
+    fin[f] = make_int4(0, 0, 0, 0);
+    mbar_arrive(bar_ffull + f * 8);
   }
 
-  if (p.dbg && lane == 0) {
-    unsigned long long t2;
+  if (p.dbg && threadIdx.x == 0) {
+    unsigned long long t1;
     unsigned smid;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t2));
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
     asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
-    long long* d = p.dbg + 6 * (int64_t)worker;
-    d[0] = smid; d[1] = (long long)dbg_t0; d[2] = (long long)dbg_t1; d[3] = (long long)t2;
-    d[4] = dbg_static + 1; d[5] = produced;
-  }
-  // ---- exit: the last worker out re-arms the pool ticket for the next launch ----------------------
-  if (lane == 0) {
-    const int nworkers = gridDim.x * kWarps;
-    if (atomicAdd(ticket + 1, 1) == nworkers - 1) {
-      ticket[0] = 0;
-      ticket[1] = 0;
-    }
+    long long* d = p.dbg + 6 * (int64_t)blockIdx.x;
+    d[0] = smid; d[1] = (long long)dbg_t0; d[2] = (long long)t1; d[3] = units_done; d[5] = (long long)dbg_first;
   }
 }
 
@@ -656,13 +770,13 @@ EncodeTiledFn get_encode_fn() {
 struct MapKey {
   const void* base;
   int64_t sb, sh, ss;
-  int32_t nb, nh, hd;
+  int32_t nh, hd;
   bool operator==(const MapKey& o) const { return memcmp(this, &o, sizeof(MapKey)) == 0; }
 };
 struct MapEntry {
   MapKey key;
   CUtensorMap map;
-  int pos_head, pos_block;
+  int pos_head;
   bool used;
 };
 constexpr int kMapCache = 64;
@@ -670,100 +784,112 @@ MapEntry g_maps[kMapCache];
 int g_map_next = 0;
 std::mutex g_map_mu;
 
-// Builds (or fetches) the 4-D tensor map of one K or V plane: dim0 = head_dim columns
-// (box 64 = 128 bytes, SWIZZLE_128B), dims 1..3 = {slot, head, block} ordered by ascending
-// stride; the box covers the 16 slots of one (block, head).
-int get_map(const void* base, const PaDecodeParams& p, CUtensorMap* out, int* pos_head, int* pos_block) {
+// Builds (or fetches) the 5-D tensor map of one K or V plane:
+//   dim0 = 64 head_dim columns (128 bytes, SWIZZLE_128B), dim1 = the 16 slots of a block,
+//   dim2 = the D / 64 column halves of a row (stride 128 bytes), dims 3, 4 = {head, block} by
+//   ascending stride.  One box = {64, 16, D / 64, 1, 1} = the whole [16 x D] tile of one
+//   (block, head), landing in shared memory as [half][slot][128 B] - one TMA instruction per tile.
+int get_map(const void* base, const PaDecodeParams& p, CUtensorMap* out, int* pos_head) {
   MapKey key;
   memset(&key, 0, sizeof(key));
   key.base = base;
   key.sb = p.kv_stride_block; key.sh = p.kv_stride_head; key.ss = p.kv_stride_slot;
-  key.nb = 0; key.nh = p.num_kv_heads; key.hd = p.head_dim;
+  key.nh = p.num_kv_heads; key.hd = p.head_dim;
   std::lock_guard<std::mutex> lock(g_map_mu);
   for (int i = 0; i < kMapCache; ++i)
     if (g_maps[i].used && g_maps[i].key == key) {
-      *out = g_maps[i].map; *pos_head = g_maps[i].pos_head; *pos_block = g_maps[i].pos_block;
+      *out = g_maps[i].map; *pos_head = g_maps[i].pos_head;
       return 0;
     }
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) return -5;
-  struct Dim { int64_t stride; uint64_t size; uint32_t box; int what; };   // what: 0 slot, 1 head, 2 block
   // The block extent is deliberately the largest the strides allow: block ids are validated by
   // the caller's allocator, and TMA zero-fills anything out of range instead of faulting.
-  Dim d[3] = {{p.kv_stride_slot, (uint64_t)kBS, (uint32_t)kBS, 0},
-              {p.kv_stride_head, (uint64_t)p.num_kv_heads, 1u, 1},
-              {p.kv_stride_block, (uint64_t)1 << 31, 1u, 2}};
-  for (int i = 0; i < 3; ++i)
-    for (int j = i + 1; j < 3; ++j)
-      if (d[j].stride < d[i].stride) { Dim t = d[i]; d[i] = d[j]; d[j] = t; }
-  cuuint64_t gdim[4] = {(cuuint64_t)p.head_dim, d[0].size, d[1].size, d[2].size};
-  cuuint64_t gstr[3] = {(cuuint64_t)d[0].stride * 2, (cuuint64_t)d[1].stride * 2, (cuuint64_t)d[2].stride * 2};
-  cuuint32_t box[4] = {64, d[0].box, d[1].box, d[2].box};
-  cuuint32_t estr[4] = {1, 1, 1, 1};
+  const bool head_first = p.kv_stride_head <= p.kv_stride_block;
+  const uint64_t halves = (uint64_t)p.head_dim / 64;
+  cuuint64_t gdim[5] = {64, (cuuint64_t)kBS, halves, 0, 0};
+  cuuint64_t gstr[4] = {(cuuint64_t)p.kv_stride_slot * 2, 128, 0, 0};
+  const cuuint64_t head_dim_sz = (cuuint64_t)p.num_kv_heads, blk_dim_sz = (cuuint64_t)1 << 31;
+  if (head_first) {
+    gdim[3] = head_dim_sz; gstr[2] = (cuuint64_t)p.kv_stride_head * 2;
+    gdim[4] = blk_dim_sz;  gstr[3] = (cuuint64_t)p.kv_stride_block * 2;
+  } else {
+    gdim[3] = blk_dim_sz;  gstr[2] = (cuuint64_t)p.kv_stride_block * 2;
+    gdim[4] = head_dim_sz; gstr[3] = (cuuint64_t)p.kv_stride_head * 2;
+  }
+  cuuint32_t box[5] = {64, (cuuint32_t)kBS, (cuuint32_t)halves, 1, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   CUtensorMap m;
-  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstr, box, estr,
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), gdim, gstr, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return -5;
-  int ph = 0, pb = 0;
-  for (int i = 0; i < 3; ++i) {
-    if (d[i].what == 1) ph = i + 1;
-    if (d[i].what == 2) pb = i + 1;
-  }
   MapEntry& e = g_maps[g_map_next];
   g_map_next = (g_map_next + 1) % kMapCache;
-  e.key = key; e.map = m; e.pos_head = ph; e.pos_block = pb; e.used = true;
-  *out = m; *pos_head = ph; *pos_block = pb;
+  e.key = key; e.map = m; e.pos_head = head_first ? 3 : 4; e.used = true;
+  *out = m; *pos_head = e.pos_head;
   return 0;
 }
 
-template <int HD, int NT>
+// per-warp ring depth that fits the shared-memory budget
+int stages_for(int hd, int g, int batch) {
+  const int stage = 2 * (hd / 64) * kBS * 128;
+  const int fixed = (int)smem_layout(hd, g, 0, batch).total;
+  const int r = (kSmemBudget - fixed) / (kConsumers * stage);
+  return r > kMaxStages ? kMaxStages : r;
+}
+
+template <int HD>
 int launch(const PaDecodeParams& p, const CUtensorMap& mk, const CUtensorMap& mv, int num_sms, cudaStream_t stream) {
-  constexpr int STAGE_BYTES = 2 * (HD / 64) * kBS * 128;
-  const size_t smem = 1024 + (size_t)kWarps * kStages * STAGE_BYTES + kWarps * kStages * (8 + 32) + 40 * 4 +
-                      (size_t)(p.batch + 1) * 4 + 16;
-  auto kern = pa_decode_tma_kernel<HD, NT>;
+  const size_t smem = smem_layout(HD, p.group, p.num_stages, p.batch).total;
+  auto kern = pa_decode_ws_kernel<HD>;
   static bool attr_set = false;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) return -5;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess) return -5;
     attr_set = true;
   }
-  if (smem > 227 * 1024) return -2;
-  kern<<<num_sms, kWarps * 32, smem, stream>>>(mk, mv, p);
+  if (smem > (size_t)kSmemBudget) return -2;
+  kern<<<num_sms, kThreads, smem, stream>>>(mk, mv, p);
   return cudaGetLastError() == cudaSuccess ? 0 : -5;
 }
 
 }  // namespace
 
-int pa_decode_tma_workers(int num_sms) { return num_sms * kWarps; }
-int pa_decode_tma_nc_max(int num_sms) { return 8 * num_sms * kWarps; }
-int pa_decode_tma_group() { return kGroup; }
 int pa_decode_tma_header_ints() { return kHeaderInts; }
+
+// Upper bound on work units (= partial slots) for any seq_lens: sum_s Hkv * ceil(nblk_s / C) <=
+// total / C + segments <= target_units + segments.
+int64_t pa_decode_tma_max_units(int batch, int num_kv_heads, int target_units) {
+  return (int64_t)target_units + (int64_t)batch * num_kv_heads;
+}
 
 bool pa_decode_tma_supported(const PaDecodeParams& p, int dtype) {
   if (dtype != 0) return false;                                   // bf16 only
   if (p.block_size != kBS) return false;
   if (p.head_dim != 64 && p.head_dim != 128) return false;
-  if (p.group > 16) return false;
-  if (p.batch > PA_MAX_BATCH_SMEM) return false;
+  if (p.group > 8) return false;
+  if (p.batch > kMaxBatch) return false;
   if ((reinterpret_cast<uintptr_t>(p.k) | reinterpret_cast<uintptr_t>(p.v)) & 15) return false;
   if ((p.kv_stride_block | p.kv_stride_head | p.kv_stride_slot) & 7) return false;   // 16-byte strides
   if (p.kv_stride_block <= 0 || p.kv_stride_head <= 0 || p.kv_stride_slot <= 0) return false;
-  if ((reinterpret_cast<uintptr_t>(p.q) & 3) || ((p.q_stride_b | p.q_stride_h) & 1)) return false;
+  // Q rows of a KV head are fetched with one bulk copy: contiguous heads, 16-byte aligned groups
+  if ((reinterpret_cast<uintptr_t>(p.q) & 15) || p.q_stride_h != p.head_dim || (p.q_stride_b & 7)) return false;
+  if ((reinterpret_cast<uintptr_t>(p.out) & 3) || ((p.o_stride_b | p.o_stride_h) & 1)) return false;
+  if (stages_for(p.head_dim, p.group, p.batch) < 2) return false;
   return true;
 }
 
 int pa_launch_decode_tma(const PaDecodeParams& p_in, int num_sms, cudaStream_t stream) {
   PaDecodeParams p = p_in;
   CUtensorMap mk, mv;
-  int ph, pb;
-  int rc = get_map(p.k, p, &mk, &ph, &pb);
+  int ph;
+  int rc = get_map(p.k, p, &mk, &ph);
   if (rc) return rc;
-  rc = get_map(p.v, p, &mv, &ph, &pb);
+  rc = get_map(p.v, p, &mv, &ph);
   if (rc) return rc;
   p.pos_head = ph;
-  p.pos_block = pb;
-  const int nt = (p.group + 7) / 8;
-  if (p.head_dim == 128) return nt == 1 ? launch<128, 1>(p, mk, mv, num_sms, stream) : launch<128, 2>(p, mk, mv, num_sms, stream);
-  return nt == 1 ? launch<64, 1>(p, mk, mv, num_sms, stream) : launch<64, 2>(p, mk, mv, num_sms, stream);
+  const int fit = stages_for(p.head_dim, p.group, p.batch);
+  p.num_stages = (p.num_stages > 0 && p.num_stages < fit) ? p.num_stages : fit;
+  if (p.head_dim == 128) return launch<128>(p, mk, mv, num_sms, stream);
+  return launch<64>(p, mk, mv, num_sms, stream);
 }
