@@ -1,0 +1,172 @@
+"""Engine call site: puts the B200 paged-attention path under the reference's
+``05_mini_vllm/mini_vllm.py`` engine loop WITHOUT editing that file.
+
+    import mini_vllm                                  # the reference module, unmodified
+    from vllm_from_scratch_b200 import engine_adapter
+    engine = mini_vllm.MiniVLLM(..., device='cuda')
+    engine_adapter.install(engine)
+    engine.generate(prompts)
+
+What is replaced (reference lines, relative to 05_mini_vllm/mini_vllm.py):
+  * step 3 of ``SelfAttention.forward`` - the flat KV scatter ``k_cache_flat[slot_mapping] = k``
+    (:421-427) -> ``reshape_and_cache`` ('bshd' layout, the model's own buffers, no copy);
+  * step 4 (:429-485) - per-request attention.  The reference's decode branch attends over flat
+    slot 0 only and ignores the block table (acknowledged in its comments, :462-471), and its
+    prefill branch ignores earlier chunks of a chunked prefill (:437-458).  Here every query token
+    attends causally over its request's whole history, read THROUGH the block table:
+    decode tokens -> one ``paged_attention_decode_batched`` launch for all decode requests of the
+    step, prefill chunks -> ``paged_attention_prefill_chunk``.
+What is kept: QKV projection, RoPE, output projection (the module's own weights and ``rope``),
+``Scheduler``, ``BlockAllocator``, ``Sampler``, ``MiniTransformer`` - untouched.
+
+The model's ``forward`` is not given block tables (:731-748), so ``install`` wraps
+``engine.scheduler.schedule`` and keeps, per step, the "attention metadata" of what was
+scheduled (block tables, chunk start positions, context lengths) - the side channel vLLM calls
+``attn_metadata``.
+
+The adapter is duck-typed on the reference's attribute names and never imports the reference.
+``ops`` is the kernel namespace (default: this package's CUDA module, which has no CPU
+fallback); tests inject an oracle-backed namespace to check the plumbing against the real
+reference engine on CPU.
+"""
+from __future__ import annotations
+
+import types
+from dataclasses import dataclass, field
+from typing import Any, List, Optional
+
+import torch
+
+
+@dataclass
+class StepMetadata:
+    """What the scheduler handed to the model this step, in scheduling order."""
+    num_tokens: List[int] = field(default_factory=list)      # tokens fed per request
+    start_pos: List[int] = field(default_factory=list)       # position of the first of them
+    is_prefill: List[bool] = field(default_factory=list)
+    block_tables: List[List[int]] = field(default_factory=list)
+    # device-side forms, built once per step and shared by every layer
+    decode_rows: Optional[torch.Tensor] = None               # int64 [Bd] token index of each decode request
+    decode_block_tables: Optional[torch.Tensor] = None       # int32 [Bd, max_blocks]
+    decode_ctx_lens: Optional[torch.Tensor] = None           # int32 [Bd] = position + 1
+    prefill_chunks: List[tuple] = field(default_factory=list)   # (token offset, n, start_pos, int32 block table)
+
+
+def _build_metadata(scheduled, device) -> StepMetadata:
+    md = StepMetadata()
+    offset = 0
+    dec_rows, dec_bts, dec_lens = [], [], []
+    for sched in scheduled:
+        n = len(sched.tokens)
+        start = int(sched.positions[0])
+        bt = [int(b) for b in sched.request.block_table]
+        md.num_tokens.append(n)
+        md.start_pos.append(start)
+        md.is_prefill.append(bool(sched.is_prefill))
+        md.block_tables.append(bt)
+        if sched.is_prefill:
+            md.prefill_chunks.append((offset, n, start, torch.tensor(bt, dtype=torch.int32).to(device)))
+        else:
+            if n != 1:
+                raise ValueError("a decode request feeds exactly one token per step")
+            dec_rows.append(offset)
+            dec_bts.append(bt)
+            dec_lens.append(start + 1)
+        offset += n
+    if dec_rows:
+        width = max(len(b) for b in dec_bts)
+        table = torch.zeros(len(dec_bts), max(width, 1), dtype=torch.int32)
+        for i, b in enumerate(dec_bts):
+            table[i, :len(b)] = torch.tensor(b, dtype=torch.int32)
+        md.decode_rows = torch.tensor(dec_rows, dtype=torch.int64).to(device)
+        md.decode_block_tables = table.to(device)
+        md.decode_ctx_lens = torch.tensor(dec_lens, dtype=torch.int32).to(device)
+    return md
+
+
+def _rotate_half(x: torch.Tensor) -> torch.Tensor:
+    half = x.shape[-1] // 2
+    return torch.cat([-x[..., half:], x[..., :half]], dim=-1)
+
+
+def _default_ops():
+    from . import paged_attention
+    return paged_attention
+
+
+def _attention_forward(attn, engine, x, positions, kv_cache, slot_mapping, seq_lens, is_prefill):
+    """Replacement for ``SelfAttention.forward`` (mini_vllm.py:394-487), bound per module."""
+    state = engine._pa_b200
+    md: StepMetadata = state["meta"]
+    ops = state["ops"]
+    if md is None or md.num_tokens != [int(s) for s in seq_lens] or md.is_prefill != [bool(p) for p in is_prefill]:
+        raise RuntimeError("engine_adapter: the model was called with a batch the wrapped scheduler did not produce")
+    t = x.shape[0]
+    h, d = attn.num_heads, attn.head_dim
+
+    # steps 1-2 of the reference forward, unchanged: QKV projection and RoPE (:408-419)
+    q, k, v = attn.qkv(x).chunk(3, dim=-1)
+    q, k, v = q.reshape(t, h, d), k.reshape(t, h, d), v.reshape(t, h, d)
+    cos, sin = attn.rope(positions)
+    cos, sin = cos.unsqueeze(1), sin.unsqueeze(1)
+    q = (q * cos + _rotate_half(q) * sin).contiguous()
+    k = (k * cos + _rotate_half(k) * sin).contiguous()
+    v = v.contiguous()
+
+    # step 3: KV slot write into the model's own [NB, BS, H, D] buffers (:421-427)
+    k_cache, v_cache = kv_cache
+    cache = (k_cache, v_cache)
+    ops.reshape_and_cache(k, v, cache, slot_mapping)
+
+    # step 4: attention through the block tables
+    out = torch.empty((t, h, d), dtype=q.dtype, device=q.device)
+    if md.decode_rows is not None:
+        q_dec = q.index_select(0, md.decode_rows)
+        o_dec = ops.paged_attention_decode_batched(q_dec, cache, md.decode_block_tables, md.decode_ctx_lens)
+        out.index_copy_(0, md.decode_rows, o_dec)
+    for offset, n, start, bt in md.prefill_chunks:
+        out[offset:offset + n] = ops.paged_attention_prefill_chunk(q[offset:offset + n], cache, bt, start)
+    return attn.out_proj(out.reshape(t, h * d))
+
+
+def install(engine: Any, ops: Any = None) -> Any:
+    """Route ``engine``'s attention through the paged-attention kernels.  Idempotent."""
+    if getattr(engine, "_pa_b200", None) is not None:
+        return engine
+    ops = ops or _default_ops()
+    layers = list(engine.model.layers)
+    state = {"ops": ops, "meta": None, "orig_schedule": engine.scheduler.schedule,
+             "orig_forwards": [layer.attn.forward for layer in layers]}
+    engine._pa_b200 = state
+    device = engine.device
+
+    def schedule_with_metadata():
+        scheduled = state["orig_schedule"]()
+        state["meta"] = _build_metadata(scheduled, device) if scheduled else None
+        return scheduled
+
+    engine.scheduler.schedule = schedule_with_metadata
+    for layer in layers:
+        attn = layer.attn
+
+        def forward(self, x, positions, kv_cache, slot_mapping, seq_lens, is_prefill, _engine=engine):
+            return _attention_forward(self, _engine, x, positions, kv_cache, slot_mapping, seq_lens, is_prefill)
+
+        attn.forward = types.MethodType(forward, attn)
+    return engine
+
+
+def uninstall(engine: Any) -> None:
+    state = getattr(engine, "_pa_b200", None)
+    if state is None:
+        return
+    engine.scheduler.schedule = state["orig_schedule"]
+    for layer, fwd in zip(engine.model.layers, state["orig_forwards"]):
+        layer.attn.forward = fwd
+    engine._pa_b200 = None
+
+
+def current_metadata(engine: Any) -> Optional[StepMetadata]:
+    """The metadata of the step being executed (for tests and for swap / copy drivers)."""
+    state = getattr(engine, "_pa_b200", None)
+    return None if state is None else state["meta"]
