@@ -52,7 +52,11 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
+    ap.add_argument("--shard", default="seq", choices=["seq", "head"],
+                    help="N > 1: 'seq' = every rank its own sequences (weak scaling, no collective); 'head' = "
+                         "every rank Hkv / N KV heads of the SAME batch + one NCCL all-gather of the outputs "
+                         "(strong scaling; default workload c3)")
     ap.add_argument("--layers", type=int, default=0, help="per-layer caches the loop rotates over")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (default min(steps, 300))")
     ap.add_argument("--ramp-ms", type=float, default=300.0, help="untimed clock ramp before the warm-up steps")
@@ -214,18 +218,32 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
 
-    wl = WORKLOADS[args.workload]
+    head_mode = args.shard == "head" and world > 1
+    wl_name = args.workload or ("c3" if head_mode else "c2")
+    wl = WORKLOADS[wl_name]
     b, ctx, hq, hkv, d, bs, def_layers, desc = wl
     layers = args.layers or def_layers
-    pool, bts_h, lens_h, q_h, k_h, v_h, slots_h = make_workload(torch, dev, wl, layers, seed=1234 + rank)
+    gather = None
+    if head_mode:
+        # KV-head sharding: this rank holds Hkv / N heads of every block and the matching query heads;
+        # block tables are identical on all ranks (same seed)
+        from vllm_from_scratch_b200 import sharding as S
+        hq_full = hq
+        hkv, hq = len(S.shard_kv_heads(hkv, world, rank)), len(S.shard_q_heads(hq, hkv, world, rank))
+        wl = (b, ctx, hq, hkv, d, bs, def_layers, desc)
+        gather = S.HeadGather(b, hq_full, d, torch.bfloat16, dev, world=world, rank=rank)
+    pool, bts_h, lens_h, q_h, k_h, v_h, slots_h = make_workload(torch, dev, wl, layers,
+                                                                seed=1234 + (0 if head_mode else rank))
     bts, lens, q = bts_h.to(dev), lens_h.to(dev), q_h.to(dev)
-    out = torch.empty_like(q)
+    out = gather.local_out() if head_mode else torch.empty_like(q)
     ws = P.new_decode_workspace(b, hq, hkv, d, dev)
     caches = [pool.layer(i) for i in range(layers)]
     kv_bytes, io_bytes = algorithmic_bytes(b, ctx, hq, hkv, d, bs)
 
     def step(i):
         P.paged_attention_decode_batched(q, caches[i % layers], bts, lens, out=out, workspace=ws)
+        if head_mode:
+            gather.all_gather()             # the kernel wrote its slice of the gather buffer in place
 
     def barrier():
         if world > 1:
@@ -275,37 +293,34 @@ def run_ours(args):
     red_avg = sum(red_ms[:got]) / got
 
     # ---- e2e: host buffers in, host buffer out, through the public Python API ----------------
-    # The step's inputs (q, new K / V rows, their slots, block tables, sequence lengths) sit in ONE
-    # pinned staging buffer and cross PCIe as ONE copy; the result comes back as one copy.
+    # graph.DecodeStep: the step's inputs (q, new K / V rows, their slots, block tables, sequence
+    # lengths) sit in ONE pinned staging buffer and cross PCIe as ONE copy; H2D -> reshape_and_cache
+    # -> decode -> D2H(out) is one captured CUDA graph per layer cache; the host waits for the result
+    # every step.
+    from vllm_from_scratch_b200.graph import DecodeStep
     ne2e = args.e2e_steps or min(args.steps, 300)
-    parts = [("q", q_h), ("k", k_h), ("v", v_h), ("slots", slots_h), ("bts", bts_h), ("lens", lens_h)]
-    offs, at = {}, 0
-    for name, t in parts:
-        at = (at + 255) // 256 * 256
-        offs[name] = at
-        at += t.numel() * t.element_size()
-    stage_h = torch.empty(at, dtype=torch.uint8).pin_memory()
-    stage_d = torch.empty(at, dtype=torch.uint8, device=dev)
-
-    def view(buf, name, like):
-        n = like.numel() * like.element_size()
-        return buf[offs[name]:offs[name] + n].view(like.dtype).view(like.shape)
-
-    for name, t in parts:
-        view(stage_h, name, t).copy_(t)
-    q_d, k_d, v_d = view(stage_d, "q", q_h), view(stage_d, "k", k_h), view(stage_d, "v", v_h)
-    s_d, bt_d, ln_d = view(stage_d, "slots", slots_h), view(stage_d, "bts", bts_h), view(stage_d, "lens", lens_h)
-    out_p = torch.empty(q_h.shape, dtype=q_h.dtype).pin_memory()
-    h2d = sum(t.numel() * t.element_size() for _, t in parts)
-    d2h = out_p.numel() * out_p.element_size()
+    steps_e2e = []
+    for c in caches:
+        st = DecodeStep(c, b, hq, bts_h.shape[1], write_kv=True, out=out if head_mode else None)
+        st.host["q"].copy_(q_h)
+        st.host["k"].copy_(k_h)
+        st.host["v"].copy_(v_h)
+        st.host["slots"].copy_(slots_h)
+        st.host["block_tables"].copy_(bts_h)
+        st.host["seq_lens"].copy_(lens_h)
+        if not head_mode:
+            st.capture()
+        steps_e2e.append(st)
+    h2d, d2h = steps_e2e[0].h2d_bytes, steps_e2e[0].d2h_bytes
 
     def e2e_step(i):
-        stage_d.copy_(stage_h, non_blocking=True)
-        cache = caches[i % layers]
-        P.reshape_and_cache(k_d, v_d, cache, s_d)                    # this step's KV slot write
-        P.paged_attention_decode_batched(q_d, cache, bt_d, ln_d, out=out, workspace=ws)
-        out_p.copy_(out, non_blocking=True)
-        torch.cuda.synchronize()                                      # the caller reads out_p now
+        st = steps_e2e[i % layers]
+        st.replay()
+        if head_mode:
+            gather.all_gather()
+        st.wait()                                                     # the caller reads st.out now
+        if head_mode:
+            torch.cuda.current_stream().synchronize()
 
     for i in range(5):
         e2e_step(i)
@@ -325,20 +340,24 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total, ms_e2e, dec_avg, red_avg = t.tolist()
     ms_step = ms_total / args.steps
-    value = world * b / (ms_step * 1e-3)
-    e2e_value = world * b / (ms_e2e / ne2e * 1e-3)
+    seqs = b if head_mode else world * b                  # head mode: all ranks work on the SAME batch
+    value = seqs / (ms_step * 1e-3)
+    e2e_value = seqs / (ms_e2e / ne2e * 1e-3)
     kv_gbs = world * kv_bytes / (ms_step * 1e-3) / 1e9
     peak, peak_src = peak_hbm()
     achieved = (kv_bytes + io_bytes) / (dec_avg * 1e-3) / 1e9
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "strong" if head_mode else "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": desc, "seqs_per_gpu": b, "context": ctx, "num_q_heads": hq, "num_kv_heads": hkv,
                    "head_dim": d, "block_size": bs, "kv_layout": "[2, L, NB, Hkv, BS, D] (reference pool)",
                    "block_tables": "seeded randperm, fully scattered",
-                   "parallelism": f"sequence-sharded x{world}, one pool per GPU, no collective",
+                   "parallelism": (f"KV-head-sharded x{world}: {hkv} KV / {hq} Q heads per GPU, one NCCL "
+                                   f"all-gather of [B, Hq/{world}, D] per step" if head_mode else
+                                   f"sequence-sharded x{world}, one pool per GPU, no collective"),
                    "l2": f"inputs larger than L2: loop rotates over {layers} per-layer caches of "
                          f"{kv_bytes / 2**20:.0f} MiB each",
                    "step": "one attention-layer decode call (one fused split-K + merge kernel) over the batch"},
@@ -346,14 +365,17 @@ def run_ours(args):
         "pct_of_8tbs_per_gpu": 100.0 * kv_gbs / world / NOMINAL_HBM_GBS,
         "kv_bytes_per_step_per_gpu": kv_bytes,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
+                     "traffic": ncu_traffic(wl_name), "peak_source": peak_src,
                      "kernel": "pa_decode_ws_kernel<128>", "kernel_ms": dec_avg, "reduce_kernel_ms": red_avg,
                      "algorithmic_bytes_per_launch": kv_bytes + io_bytes,
                      "frac_of_nominal_8tbs": achieved / NOMINAL_HBM_GBS, "launches_timed": got},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": ne2e, "ms_per_step": ms_e2e / ne2e,
-                "what": "pinned host q/k/v/slots/block tables/seq lens -> one H2D -> reshape_and_cache -> decode -> "
-                        "D2H out, synchronised every step; the KV pool is resident state"},
+                "what": "graph.DecodeStep: every input of the step starts in pinned host memory; new K / V rows, "
+                        "slots, block tables and seq lens cross PCIe as one staged H2D copy, the decode kernel reads "
+                        "q from and writes out to pinned host memory in place (zero-copy over PCIe; both counted in "
+                        "the byte totals); copy -> reshape_and_cache -> decode is one CUDA graph and the host waits "
+                        "for the result every step; the KV pool is resident state"},
         "gpu_launches": args.steps,       # timed region: one decode launch per step (the fast path has no reduce launch)
         "clocks": clocks,
     }
@@ -428,7 +450,7 @@ def run_reference(args):
 
     import torch
     torch.set_num_threads(1)
-    wl = WORKLOADS[args.workload]
+    wl = WORKLOADS[args.workload or ("c3" if args.shard == "head" and args.gpus > 1 else "c2")]
     b, ctx, hq, hkv, d, bs, _, desc = wl
     cores = max(1, min(os.cpu_count() or 1, b, 64))
     nseq = cores                                   # sample: one sequence per core per step

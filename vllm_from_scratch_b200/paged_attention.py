@@ -42,6 +42,18 @@ def _require_cuda(t: torch.Tensor, name: str) -> None:
             "allocate the tensor on a CUDA device")
 
 
+def _require_cuda_or_pinned(t: torch.Tensor, name: str) -> None:
+    """Device tensors, or PINNED host tensors: under unified addressing the kernels read / write
+    page-locked host memory in place over PCIe (zero-copy), which saves a staging copy and its
+    launch latency for small per-step operands (the decode query and output)."""
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name} must be a torch.Tensor, got {type(t).__name__}")
+    if not t.is_cuda and not t.is_pinned():
+        raise RuntimeError(
+            f"{name} is pageable host memory: the B200 paged-attention path has no CPU fallback; "
+            "allocate it on a CUDA device (or pin it for zero-copy access)")
+
+
 def _stream_ptr(stream: Optional[torch.cuda.Stream] = None) -> int:
     return (stream or torch.cuda.current_stream()).cuda_stream
 
@@ -256,10 +268,12 @@ def paged_attention_decode_batched(query: torch.Tensor, kv_cache: KvCacheArg, bl
 
     query ``[B, Hq, D]``; block_tables int32 ``[B, max_blocks]`` and seq_lens int32 ``[B]`` on the
     device (no host sync on the launch path); entries past ``ceil(seq_len / BS)`` are never read;
-    ``seq_len == 0`` gives zeros.  Output dtype/device = query's.  A caller-provided ``workspace``
-    must come from ``new_decode_workspace`` (zero-initialised counter header)."""
+    ``seq_len == 0`` gives zeros.  Output dtype = query's, on the cache's device unless ``out`` is
+    given.  ``query`` / ``out`` may also be PINNED host tensors (read / written in place over PCIe).
+    A caller-provided ``workspace`` must come from ``new_decode_workspace`` (zero-initialised
+    counter header)."""
     desc, kplane = _describe_cache(kv_cache)
-    _require_cuda(query, "query")
+    _require_cuda_or_pinned(query, "query")
     _require_cuda(block_tables, "block_tables")
     _require_cuda(seq_lens, "seq_lens")
     if query.dim() != 3:
@@ -281,18 +295,18 @@ def paged_attention_decode_batched(query: torch.Tensor, kv_cache: KvCacheArg, bl
         query = query.contiguous()
     seq_lens = seq_lens.contiguous()
     if out is None:
-        out = torch.empty((b, hq, d), dtype=query.dtype, device=query.device)
+        out = torch.empty((b, hq, d), dtype=query.dtype, device=kplane.device)
     else:
-        _require_cuda(out, "out")
+        _require_cuda_or_pinned(out, "out")
         if out.shape != (b, hq, d) or out.dtype != query.dtype or (out.stride(2) != 1 and d > 1):
             raise ValueError("out must be [B, Hq, D] with the query's dtype and a contiguous last axis")
     lib = _lib.load()
     need = lib.pa_decode_workspace_bytes(b, hq, desc.num_kv_heads, d)
     if workspace is None:
-        workspace = _workspace(query.device, need)
+        workspace = _workspace(kplane.device, need)
     elif not workspace.is_cuda or workspace.numel() * workspace.element_size() < need:
         raise ValueError(f"workspace must be a CUDA tensor of at least {need} bytes")
-    with _DeviceOf(query):
+    with _DeviceOf(kplane):
         rc = lib.pa_decode(query.data_ptr(), query.stride(0), query.stride(1),
                            out.data_ptr(), out.stride(0), out.stride(1),
                            ctypes.byref(desc), block_tables.data_ptr(), block_tables.stride(0),
