@@ -214,8 +214,11 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        import datetime
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on stdout when NCCL_DEBUG is set: keep stdout to the one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     lib = _lib.load()
 
     head_mode = args.shard == "head" and world > 1
@@ -493,6 +496,9 @@ def run_reference(args):
 
 def main():
     args = parse_args()
+    if os.environ.get("BENCH_DEBUG"):
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ.get("BENCH_DEBUG_AFTER", "60")), exit=True)
     if args.impl == "reference":
         run_reference(args)
     else:
