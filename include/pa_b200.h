@@ -151,10 +151,14 @@ int pa_swap_blocks(void* dst_base, int64_t dst_plane_stride_bytes, int64_t dst_b
  *      table - the KV of the chunk must already be in the cache, i.e. call
  *      pa_reshape_and_cache first) ------------------------------------------------
  * q / out [num_tokens, num_q_heads, D].  One sequence per call.
- * Round-1 implementation: every query token is a decode "sequence" of length
- * start_pos + i + 1 over the shared block table (same kernels, same numerics
- * as pa_decode); a dedicated tcgen05 prefill kernel is the next row of the
- * scope table.                                                               */
+ * Two implementations behind this entry:
+ *  - tensor-core path (bf16, block_size 16, head_dim 64 / 128, g a power of
+ *    two <= 16, 16-byte aligned strides): pa_prefill_tc_kernel, tcgen05.mma
+ *    with TMEM accumulators, K / V tiles gathered by TMA through the block
+ *    table (csrc/pa_prefill_tc.cu);
+ *  - everything else (fp32 caches, the engine's toy head sizes): every query
+ *    token is a decode "sequence" of length start_pos + i + 1 over the shared
+ *    block table (same kernels and numerics as pa_decode).                   */
 size_t pa_prefill_workspace_bytes(int32_t num_tokens, int32_t num_q_heads,
                                   int32_t num_kv_heads, int32_t head_dim);
 
@@ -164,6 +168,31 @@ int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
                int32_t start_pos, int32_t num_tokens, int32_t num_q_heads,
                void* workspace, size_t workspace_bytes,
                void* stream);
+
+/* ---- varlen prefill: a BATCH of query chunks in one launch (the engine's mixed
+ *      chunked-prefill + decode step, mini_vllm.py:437-481; varlen layout as in
+ *      BLOG_PART2_V2.md:1104-1141) ---------------------------------------------
+ * q / out [total_tokens, num_q_heads, D], the chunks of the sequences packed
+ * back to back: sequence s owns tokens [cu_q_lens[s], cu_q_lens[s + 1]) which
+ * sit at positions [ctx_lens[s] - q_len, ctx_lens[s]) of its context and
+ * attend causally to [0, pos] through block_tables[s].  q_len = 1 is a decode
+ * token.  cu_q_lens int32 [batch + 1], ctx_lens int32 [batch] on the DEVICE;
+ * max_q_len (host) >= every q_len sizes the grid.  Tensor-core path only:
+ * PA_ERR_UNSUPPORTED for shapes outside it (see pa_prefill); the caller then
+ * loops pa_prefill per sequence.                                              */
+int pa_prefill_varlen(const void* q, int64_t q_stride_t, int64_t q_stride_h,
+                      void* out, int64_t o_stride_t, int64_t o_stride_h,
+                      const PaKvCache* cache,
+                      const int32_t* block_tables, int32_t bt_stride,
+                      const int32_t* cu_q_lens, const int32_t* ctx_lens,
+                      int32_t batch, int32_t max_q_len, int32_t num_q_heads,
+                      void* stream);
+/* 1 when pa_prefill / pa_prefill_varlen take the tensor-core path for this
+ * cache and head count (pointer alignment is checked per call), else 0.       */
+int pa_prefill_tc_available(const PaKvCache* cache, int32_t num_q_heads);
+/* 0 = automatic (default); 1 = force the decode-kernel formulation in
+ * pa_prefill even where the tensor-core kernel applies.  Returns the old value. */
+int pa_prefill_force_path(int path);
 
 /* ---- test / tuning hook ---------------------------------------------------
  * 0 = automatic kernel choice (default); 1 = force the generic CUDA-core

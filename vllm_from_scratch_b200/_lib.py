@@ -51,6 +51,10 @@ SIGNATURES = {
     "pa_prefill_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
     "pa_prefill": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
                            c_void_p, c_int32, c_int32, c_int32, c_void_p, c_size_t, c_void_p]),
+    "pa_prefill_varlen": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
+                                  c_void_p, c_int32, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p]),
+    "pa_prefill_tc_available": (c_int, [POINTER(PaKvCache), c_int32]),
+    "pa_prefill_force_path": (c_int, [c_int]),
     "pa_decode_set_tuning": (c_int, [c_int, c_int, c_int, c_int]),
     "pa_decode_debug_times": (c_int, [c_void_p]),
     "pa_profile_begin": (c_int, [c_int32]),

@@ -5,6 +5,7 @@
 #include <atomic>
 #include <math.h>
 #include <mutex>
+#include <string.h>
 #include <vector>
 
 #include "../../include/pa_b200.h"
@@ -257,6 +258,54 @@ extern "C" size_t pa_prefill_workspace_bytes(int32_t num_tokens, int32_t num_q_h
   return pa_decode_workspace_bytes(chunk, num_q_heads, num_kv_heads, head_dim) + align_up((size_t)chunk * 4, 256);
 }
 
+namespace {
+std::atomic<int> g_prefill_force{0};
+
+int fill_prefill_params(PaPrefillParams& p, const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out,
+                        int64_t o_stride_t, int64_t o_stride_h, const PaKvCache* cache, int32_t num_q_heads) {
+  memset(&p, 0, sizeof(p));
+  if (!cache || cache->num_kv_heads <= 0 || num_q_heads <= 0 || num_q_heads % cache->num_kv_heads) return PA_ERR_BAD_ARG;
+  p.q = q; p.out = out; p.k = cache->k; p.v = cache->v;
+  p.q_stride_t = q_stride_t; p.q_stride_h = q_stride_h; p.o_stride_t = o_stride_t; p.o_stride_h = o_stride_h;
+  p.kv_stride_block = cache->stride_block; p.kv_stride_head = cache->stride_head; p.kv_stride_slot = cache->stride_slot;
+  p.num_q_heads = num_q_heads; p.num_kv_heads = cache->num_kv_heads; p.head_dim = cache->head_dim;
+  p.group = num_q_heads / cache->num_kv_heads;
+  p.scale_log2e = (float)((1.0 / sqrt((double)cache->head_dim)) * 1.4426950408889634);
+  return PA_OK;
+}
+}  // namespace
+
+extern "C" int pa_prefill_force_path(int path) { return g_prefill_force.exchange(path); }
+
+extern "C" int pa_prefill_tc_available(const PaKvCache* cache, int32_t num_q_heads) {
+  PaPrefillParams p;
+  if (!cache || !cache->k || !cache->v) return 0;
+  if (fill_prefill_params(p, cache->k, 0, 0, cache->k, 0, 0, cache, num_q_heads) != PA_OK) return 0;
+  p.q_stride_t = p.o_stride_t = (int64_t)num_q_heads * cache->head_dim;
+  p.q_stride_h = p.o_stride_h = cache->head_dim;
+  p.batch = 1; p.max_q_len = 1;
+  return pa_prefill_tc_supported(p, cache->dtype, cache->block_size) ? 1 : 0;
+}
+
+extern "C" int pa_prefill_varlen(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t o_stride_t,
+                                 int64_t o_stride_h, const PaKvCache* cache, const int32_t* block_tables,
+                                 int32_t bt_stride, const int32_t* cu_q_lens, const int32_t* ctx_lens, int32_t batch,
+                                 int32_t max_q_len, int32_t num_q_heads, void* stream) {
+  if (batch < 0 || max_q_len < 0 || !cache) return PA_ERR_BAD_ARG;
+  if (batch == 0 || max_q_len == 0) return PA_OK;
+  if (!q || !out || !cache->k || !cache->v || !block_tables || !cu_q_lens || !ctx_lens || bt_stride < 0)
+    return PA_ERR_BAD_ARG;
+  if (sm_count() <= 0) return PA_ERR_NO_DEVICE;
+  PaPrefillParams p;
+  int rc = fill_prefill_params(p, q, q_stride_t, q_stride_h, out, o_stride_t, o_stride_h, cache, num_q_heads);
+  if (rc) return rc;
+  p.block_tables = block_tables; p.bt_stride = bt_stride;
+  p.cu_q_lens = cu_q_lens; p.ctx_lens = ctx_lens;
+  p.batch = batch; p.max_q_len = max_q_len;
+  if (!pa_prefill_tc_supported(p, cache->dtype, cache->block_size)) return PA_ERR_UNSUPPORTED;
+  return pa_launch_prefill_tc(p, static_cast<cudaStream_t>(stream));
+}
+
 extern "C" int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t o_stride_t,
                           int64_t o_stride_h, const PaKvCache* cache, const int32_t* block_table,
                           int32_t start_pos, int32_t num_tokens, int32_t num_q_heads, void* workspace,
@@ -267,6 +316,18 @@ extern "C" int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
   if (cache->dtype != PA_BF16 && cache->dtype != PA_F32) return PA_ERR_UNSUPPORTED;
   if (workspace_bytes < pa_prefill_workspace_bytes(num_tokens, num_q_heads, cache->num_kv_heads, cache->head_dim))
     return PA_ERR_WORKSPACE;
+  if (g_prefill_force.load() != 1 && q && out && block_table && cache->k && cache->v) {
+    PaPrefillParams tp;
+    if (fill_prefill_params(tp, q, q_stride_t, q_stride_h, out, o_stride_t, o_stride_h, cache, num_q_heads) == PA_OK) {
+      tp.block_tables = block_table; tp.bt_stride = 0;
+      tp.batch = 1; tp.num_tokens = num_tokens; tp.max_q_len = num_tokens;
+      tp.ctx_len_single = start_pos + num_tokens;
+      if (pa_prefill_tc_supported(tp, cache->dtype, cache->block_size)) {
+        if (sm_count() <= 0) return PA_ERR_NO_DEVICE;
+        return pa_launch_prefill_tc(tp, static_cast<cudaStream_t>(stream));
+      }
+    }
+  }
   const int es = cache->dtype == PA_F32 ? 4 : 2;
   const int chunk_cap = num_tokens < kPrefillChunk ? num_tokens : kPrefillChunk;
   // the decode workspace (with its zeroed counter header) sits at offset 0; the lens array follows it

@@ -146,3 +146,28 @@ bool pa_decode_tma_supported(const PaDecodeParams& p, int dtype);
 int pa_decode_tma_header_ints();
 int64_t pa_decode_tma_max_units(int batch, int num_kv_heads, int target_units);
 int pa_decode_generic_workers(int num_sms, int* ctas);
+
+// ---- tensor-core (tcgen05) paged prefill, pa_prefill_tc.cu --------------------------------
+// A varlen batch of query chunks: sequence s owns query tokens [cu_q_lens[s], cu_q_lens[s + 1])
+// at positions [ctx_lens[s] - q_len, ctx_lens[s]) and attends causally to positions [0, pos]
+// read through its block table (the chunk's own K / V already written by reshape-and-cache).
+// cu_q_lens == nullptr: ONE sequence of num_tokens query tokens whose context is ctx_len_single.
+struct PaPrefillParams {
+  const void* q;
+  void* out;
+  const void* k;
+  const void* v;
+  const int32_t* block_tables;
+  const int32_t* cu_q_lens;
+  const int32_t* ctx_lens;
+  int64_t q_stride_t, q_stride_h;
+  int64_t o_stride_t, o_stride_h;
+  int64_t kv_stride_block, kv_stride_head, kv_stride_slot;
+  int32_t bt_stride;
+  int32_t batch, num_tokens, ctx_len_single, max_q_len;
+  int32_t num_q_heads, num_kv_heads, head_dim, group;
+  int32_t pos_head;       // which of tensor-map dims 3 / 4 is the head axis
+  float scale_log2e;
+};
+bool pa_prefill_tc_supported(const PaPrefillParams& p, int dtype, int block_size);
+int pa_launch_prefill_tc(const PaPrefillParams& p, cudaStream_t stream);

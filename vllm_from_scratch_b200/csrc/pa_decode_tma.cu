@@ -771,6 +771,7 @@ struct MapKey {
   const void* base;
   int64_t sb, sh, ss;
   int32_t nh, hd;
+  int32_t box_halves, pad;
   bool operator==(const MapKey& o) const { return memcmp(this, &o, sizeof(MapKey)) == 0; }
 };
 struct MapEntry {
@@ -789,12 +790,16 @@ std::mutex g_map_mu;
 //   dim2 = the D / 64 column halves of a row (stride 128 bytes), dims 3, 4 = {head, block} by
 //   ascending stride.  One box = {64, 16, D / 64, 1, 1} = the whole [16 x D] tile of one
 //   (block, head), landing in shared memory as [half][slot][128 B] - one TMA instruction per tile.
-int get_map(const void* base, const PaDecodeParams& p, CUtensorMap* out, int* pos_head) {
+//   box_halves < D / 64 (the prefill kernel passes 1) makes one box a single 64-column half, so the
+//   halves of consecutive blocks can be laid out slab-major for UMMA.
+int get_map(const void* base, const PaDecodeParams& p, CUtensorMap* out, int* pos_head, int box_halves = 0) {
   MapKey key;
   memset(&key, 0, sizeof(key));
   key.base = base;
   key.sb = p.kv_stride_block; key.sh = p.kv_stride_head; key.ss = p.kv_stride_slot;
   key.nh = p.num_kv_heads; key.hd = p.head_dim;
+  if (box_halves <= 0) box_halves = p.head_dim / 64;
+  key.box_halves = box_halves;
   std::lock_guard<std::mutex> lock(g_map_mu);
   for (int i = 0; i < kMapCache; ++i)
     if (g_maps[i].used && g_maps[i].key == key) {
@@ -817,7 +822,7 @@ int get_map(const void* base, const PaDecodeParams& p, CUtensorMap* out, int* po
     gdim[3] = blk_dim_sz;  gstr[2] = (cuuint64_t)p.kv_stride_block * 2;
     gdim[4] = head_dim_sz; gstr[3] = (cuuint64_t)p.kv_stride_head * 2;
   }
-  cuuint32_t box[5] = {64, (cuuint32_t)kBS, (cuuint32_t)halves, 1, 1};
+  cuuint32_t box[5] = {64, (cuuint32_t)kBS, (cuuint32_t)box_halves, 1, 1};
   cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   CUtensorMap m;
   CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), gdim, gstr, box, estr,
@@ -856,6 +861,10 @@ int launch(const PaDecodeParams& p, const CUtensorMap& mk, const CUtensorMap& mv
 }  // namespace
 
 int pa_decode_tma_header_ints() { return kHeaderInts; }
+
+int pa_get_kv_tensor_map(const void* base, const PaDecodeParams& p, int box_halves, CUtensorMap* out, int* pos_head) {
+  return get_map(base, p, out, pos_head, box_halves);
+}
 
 // Upper bound on work units (= partial slots) for any seq_lens: sum_s Hkv * ceil(nblk_s / C) <=
 // total / C + segments <= target_units + segments.

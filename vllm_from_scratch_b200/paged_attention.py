@@ -368,6 +368,66 @@ def paged_attention_prefill_chunk(query: torch.Tensor, kv_cache: KvCacheArg, blo
     return out
 
 
+def prefill_tensor_core_available(kv_cache: KvCacheArg, num_q_heads: int) -> bool:
+    """True when prefill over this cache runs on the tcgen05 kernel (bf16, block_size 16,
+    head_dim 64 / 128, g a power of two <= 16)."""
+    desc, _ = _describe_cache(kv_cache)
+    return bool(_lib.load().pa_prefill_tc_available(ctypes.byref(desc), num_q_heads))
+
+
+def paged_attention_prefill_varlen(query: torch.Tensor, kv_cache: KvCacheArg, block_tables: torch.Tensor,
+                                   cu_q_lens: torch.Tensor, ctx_lens: torch.Tensor, max_q_len: int,
+                                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """One launch for a batch of query chunks packed back to back (the engine's mixed
+    chunked-prefill + decode step, mini_vllm.py:437-481): sequence ``s`` owns query tokens
+    ``[cu_q_lens[s], cu_q_lens[s + 1])`` at positions ``[ctx_lens[s] - q_len, ctx_lens[s])`` and
+    attends causally to ``[0, pos]`` through ``block_tables[s]``; its K / V (history and the chunk
+    itself) must already be in the cache.  ``cu_q_lens`` int32 ``[B + 1]`` and ``ctx_lens`` int32
+    ``[B]`` live on the device; ``max_q_len`` is a host int >= every chunk length.  Shapes outside
+    the tensor-core path are looped per sequence through ``paged_attention_prefill_chunk``."""
+    desc, kplane = _describe_cache(kv_cache)
+    for name, ten in (("query", query), ("block_tables", block_tables), ("cu_q_lens", cu_q_lens),
+                      ("ctx_lens", ctx_lens)):
+        _require_cuda(ten, name)
+    if query.dim() != 3 or query.shape[2] != desc.head_dim or query.dtype != kplane.dtype:
+        raise ValueError("query must be [T, Hq, D] in the cache dtype")
+    if block_tables.dim() != 2 or block_tables.dtype != torch.int32 or block_tables.stride(1) != 1:
+        raise ValueError("block_tables must be int32 [B, max_blocks] with a contiguous last axis")
+    if cu_q_lens.dtype != torch.int32 or ctx_lens.dtype != torch.int32:
+        raise ValueError("cu_q_lens and ctx_lens must be int32")
+    b = block_tables.shape[0]
+    if cu_q_lens.numel() != b + 1 or ctx_lens.numel() != b:
+        raise ValueError("cu_q_lens must have B + 1 entries and ctx_lens B")
+    t, hq, d = query.shape
+    if hq % desc.num_kv_heads:
+        raise ValueError("num_q_heads must be a multiple of num_kv_heads")
+    if query.stride(2) != 1 and d > 1:
+        query = query.contiguous()
+    if out is None:
+        out = torch.empty((t, hq, d), dtype=query.dtype, device=query.device)
+    if t == 0 or b == 0:
+        return out
+    lib = _lib.load()
+    cu = cu_q_lens.contiguous()
+    cl = ctx_lens.contiguous()
+    with _DeviceOf(query):
+        rc = lib.pa_prefill_varlen(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(),
+                                   out.stride(0), out.stride(1), ctypes.byref(desc), block_tables.data_ptr(),
+                                   block_tables.stride(0), cu.data_ptr(), cl.data_ptr(), b, int(max_q_len), hq,
+                                   _stream_ptr())
+    if rc == -2:        # PA_ERR_UNSUPPORTED: not a tensor-core shape -> per-sequence CUDA path
+        cu_h = cu.tolist()
+        cl_h = cl.tolist()
+        for s in range(b):
+            q0, q1 = cu_h[s], cu_h[s + 1]
+            if q1 > q0:
+                paged_attention_prefill_chunk(query[q0:q1], kv_cache, block_tables[s], cl_h[s] - (q1 - q0),
+                                              out=out[q0:q1])
+        return out
+    _lib.check(rc, "pa_prefill_varlen")
+    return out
+
+
 def paged_attention_prefill(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, kv_cache: torch.Tensor,
                             block_table: List[int], block_size: int) -> torch.Tensor:
     """Reference signature (paged_attention.py:104-111): write K/V of positions 0..T-1 into the
