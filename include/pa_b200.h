@@ -121,6 +121,24 @@ int pa_reshape_and_cache(const void* key, const void* value,
                          const int64_t* slot_mapping, int32_t num_tokens,
                          void* stream);
 
+/* ---- fused RoPE + QKV split + KV slot write (replaces mini_vllm.py:410-427:
+ *      chunk(3), rope(positions) (:372-375), q*cos + rotate_half(q)*sin
+ *      (:355-357, :418-419) and the two cache scatters (:424-427)) --------------
+ * qkv [num_tokens, (Hq + 2 Hkv) * D]: per token the Q heads, then the K heads,
+ *   then the V heads (qkv_stride_t in elements).  cos_table / sin_table
+ *   [max_positions, D] are the module's own cached tables (cos_cached /
+ *   sin_cached, :366-370) in the same dtype; positions int64 [num_tokens].
+ * Writes rotated Q to q_out [num_tokens, Hq, D], rotated K and plain V to the
+ *   cache slots (slot < 0 skips the cache write).  Rounds exactly where torch's
+ *   op-by-op evaluation rounds (no FMA contraction): bit-exact in fp32 and bf16. */
+int pa_rope_and_cache(const void* qkv, int64_t qkv_stride_t, int32_t num_q_heads,
+                      const void* cos_table, const void* sin_table,
+                      int64_t table_stride, int32_t max_positions,
+                      const int64_t* positions, const int64_t* slot_mapping,
+                      int32_t num_tokens,
+                      void* q_out, int64_t q_stride_t, int64_t q_stride_h,
+                      const PaKvCache* cache, void* stream);
+
 /* ---- block copy (no reference code; definitional:
  *      plane[p][dst] = plane[p][src] for every plane and pair;
  *      prose: BLOG_PART1_V2.md:748-777) --------------------------------------

@@ -168,11 +168,11 @@ class Rope(nn.Module):
         inv = 1.0 / (base ** (torch.arange(0, dim, 2).float() / dim))
         ang = torch.outer(torch.arange(max_len).float(), inv)
         ang = torch.cat([ang, ang], dim=-1)
-        self.register_buffer("cos_t", ang.cos())
-        self.register_buffer("sin_t", ang.sin())
+        self.register_buffer("cos_cached", ang.cos())
+        self.register_buffer("sin_cached", ang.sin())
 
     def forward(self, positions):
-        return self.cos_t[positions], self.sin_t[positions]
+        return self.cos_cached[positions], self.sin_cached[positions]
 
 
 class Attn(nn.Module):

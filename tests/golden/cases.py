@@ -75,3 +75,23 @@ def make_prefill_inputs(case):
     bt = torch.randperm(nb, generator=g)[:nblk].tolist()
     kv = torch.zeros(2, nb, hkv, bs, d, dtype=_dtype(dt))
     return q, k, v, kv, bt
+
+
+# (name, dtype, H, D, BS, NB, T, max_len, seed) - the engine's SelfAttention has Hq == Hkv == H
+ROPE_CASES = [
+    ("engine_default", "f32", 8, 32, 16, 8, 40, 256, 30),     # mini_vllm.py:943-954 head shape
+    ("tiny_d16", "f32", 4, 16, 16, 4, 19, 64, 31),
+    ("bf16_d128", "bf16", 2, 128, 16, 6, 70, 512, 32),
+    ("bf16_d32", "bf16", 8, 32, 4, 32, 33, 128, 33),
+]
+
+
+def make_rope_inputs(case):
+    name, dt, h, d, bs, nb, t, max_len, seed = case
+    g = torch.Generator().manual_seed(seed)
+    qkv = torch.randn(t, 3 * h * d, generator=g).to(_dtype(dt))
+    positions = torch.randint(0, max_len, (t,), generator=g)
+    slots = torch.randperm(nb * bs, generator=g)[:t]
+    k_cache = torch.randn(nb, bs, h, d, generator=g).to(_dtype(dt))
+    v_cache = torch.randn(nb, bs, h, d, generator=g).to(_dtype(dt))
+    return qkv, positions, slots, k_cache, v_cache

@@ -11,6 +11,7 @@ copied), runs them on seeded inputs and writes
     tests/golden/decode_cases.npz     reference outputs of paged_attention_decode + sha256 of inputs
     tests/golden/prefill_cases.npz    outputs of paged_attention_prefill + sha256 of inputs / written cache
     tests/golden/integer_cases.json   slot mappings, allocator traces, scheduler traces
+    tests/golden/rope_cases.npz       RoPE + QKV split + KV scatter (SelfAttention.forward steps 1b-3)
 
 Inputs are regenerated from seeds by tests/golden/cases.py (shared with the tests) and
 pinned by sha256; bf16 outputs are stored upcast to float32 (exact).  The files are small
@@ -28,8 +29,8 @@ import torch
 REF = os.environ.get("PA_REFERENCE_ROOT", "/root/reference")
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, HERE)
-from cases import (DECODE_CASES, PREFILL_CASES, make_decode_inputs, make_prefill_inputs,  # noqa: E402
-                   tensor_sha)
+from cases import (DECODE_CASES, PREFILL_CASES, ROPE_CASES, make_decode_inputs, make_prefill_inputs,  # noqa: E402
+                   make_rope_inputs, tensor_sha)
 
 
 def _import_reference():
@@ -123,10 +124,36 @@ def gen_integers(ref_pa, ref_engine):
         json.dump(js, f)
 
 
+def gen_rope(ref_engine):
+    """Steps 1b-3 of the reference SelfAttention.forward (mini_vllm.py:410-427) run with the
+    reference's own RotaryEmbedding module and rotate_half on seeded inputs."""
+    out = {}
+    for case in ROPE_CASES:
+        name, dt, h, d, bs, nb, t, max_len, seed = case
+        qkv, positions, slots, k_cache, v_cache = make_rope_inputs(case)
+        in_sha = tensor_sha(qkv, positions, slots, k_cache, v_cache)
+        rope = ref_engine.RotaryEmbedding(d, max_len=max_len).to(qkv.dtype)
+        q, k, v = qkv.chunk(3, dim=-1)
+        q, k, v = q.view(t, h, d), k.view(t, h, d), v.view(t, h, d)
+        cos, sin = rope(positions)
+        cos, sin = cos.unsqueeze(1), sin.unsqueeze(1)
+        q = q * cos + ref_engine.rotate_half(q) * sin
+        k = k * cos + ref_engine.rotate_half(k) * sin
+        k_cache.view(-1, h, d)[slots] = k
+        v_cache.view(-1, h, d)[slots] = v
+        out[f"{name}/q"] = _np(q)
+        out[f"{name}/k_cache"] = _np(k_cache)
+        out[f"{name}/v_cache"] = _np(v_cache)
+        out[f"{name}/in_sha"] = np.asarray(in_sha)
+    np.savez_compressed(os.path.join(HERE, "rope_cases.npz"), **out)
+
+
 if __name__ == "__main__":
     ref_pa, ref_engine = _import_reference()
-    gen_decode(ref_pa)
-    gen_prefill(ref_pa)
-    gen_integers(ref_pa, ref_engine)
-    for fn in ("decode_cases.npz", "prefill_cases.npz", "integer_cases.json"):
+    if "--only-rope" not in sys.argv:
+        gen_decode(ref_pa)
+        gen_prefill(ref_pa)
+        gen_integers(ref_pa, ref_engine)
+    gen_rope(ref_engine)
+    for fn in ("decode_cases.npz", "prefill_cases.npz", "integer_cases.json", "rope_cases.npz"):
         print(fn, os.path.getsize(os.path.join(HERE, fn)), "bytes")

@@ -14,7 +14,8 @@ import numpy as np
 import pytest
 import torch
 
-from cases import (DECODE_CASES, PREFILL_CASES, make_decode_inputs, make_prefill_inputs, tensor_sha)
+from cases import (DECODE_CASES, PREFILL_CASES, ROPE_CASES, make_decode_inputs, make_prefill_inputs,
+                   make_rope_inputs, tensor_sha)
 from oracle import paged_attention_oracle as O
 
 pytestmark = pytest.mark.gpu
@@ -575,3 +576,60 @@ def test_abi_status_codes(lib):
     assert lib.pa_decode(16, 1, 1, 16, 1, 1, ctypes.byref(c), 16, 1, 16, 1, 4, 16, 1 << 20, None) == -2
     c = PaKvCache(16, 16, 512, 256, 32, 1, 2, 16, 32, 1, 0)
     assert lib.pa_decode(16, 1, 1, 16, 1, 1, ctypes.byref(c), 16, 1, 16, 1, 4, 16, 64, None) == -4   # workspace
+
+
+# =========================================================================================
+# fused RoPE + QKV split + KV slot write (mini_vllm.py:410-427) - bit-exact vs torch's op-by-op result
+# =========================================================================================
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("hq,hkv,d,bs", [(8, 8, 32, 16), (4, 4, 16, 16), (32, 8, 128, 16), (2, 2, 6, 4), (8, 2, 64, 8)])
+def test_rope_and_cache_bit_exact(P, dtype, hq, hkv, d, bs):
+    g = torch.Generator().manual_seed(hq * 100 + d)
+    t, max_len = 97, 512
+    nb = (t + bs - 1) // bs + 3
+    qkv = torch.randn(t, (hq + 2 * hkv) * d, generator=g).to(dtype)
+    positions = torch.randint(0, max_len, (t,), generator=g)
+    slots = torch.randperm(nb * bs, generator=g)[:t]
+    slots[5] = -1                                                    # padding token: Q still rotates, no cache write
+    cos, sin = (x.to(dtype) for x in O.rope_tables(d, max_len))     # nn.Module.to(dtype) casts the buffers too
+    k_ref = torch.randn(nb, bs, hkv, d, generator=g).to(dtype)
+    v_ref = torch.randn(nb, bs, hkv, d, generator=g).to(dtype)
+    k_dev, v_dev = k_ref.to(DEV), v_ref.to(DEV)
+    q_ref = O.rope_split_and_cache_bshd(qkv, positions, cos, sin, k_ref, v_ref, slots, hq, hkv)
+    q_dev = P.rope_and_cache(qkv.to(DEV), positions.to(DEV), cos.to(DEV), sin.to(DEV), (k_dev, v_dev),
+                             slots.to(DEV), hq)
+    assert torch.equal(q_dev.cpu(), q_ref)
+    assert torch.equal(k_dev.cpu(), k_ref) and torch.equal(v_dev.cpu(), v_ref)
+
+
+def test_rope_and_cache_hbsd_layout_and_strided_qkv(P):
+    """Module-01 pool layout [2, NB, Hkv, BS, D] and a qkv that is a column slice of a wider buffer."""
+    g = torch.Generator().manual_seed(3)
+    t, hq, hkv, d, bs, nb, max_len = 50, 8, 2, 64, 16, 6, 128
+    wide = torch.randn(t, (hq + 2 * hkv) * d + 64, generator=g).to(torch.bfloat16)
+    qkv = wide[:, 64:]
+    positions = torch.arange(t)
+    slots = torch.randperm(nb * bs, generator=g)[:t]
+    cos, sin = (x.to(torch.bfloat16) for x in O.rope_tables(d, max_len))
+    k_ref = torch.zeros(nb, bs, hkv, d, dtype=torch.bfloat16)
+    v_ref = torch.zeros(nb, bs, hkv, d, dtype=torch.bfloat16)
+    q_ref = O.rope_split_and_cache_bshd(qkv, positions, cos, sin, k_ref, v_ref, slots, hq, hkv)
+    kv = torch.zeros(2, nb, hkv, bs, d, dtype=torch.bfloat16, device=DEV)
+    q_dev = P.rope_and_cache(wide.to(DEV)[:, 64:], positions.to(DEV), cos.to(DEV), sin.to(DEV), kv, slots.to(DEV), hq)
+    assert torch.equal(q_dev.cpu(), q_ref)
+    assert torch.equal(kv[0].cpu().permute(0, 2, 1, 3), k_ref) and torch.equal(kv[1].cpu().permute(0, 2, 1, 3), v_ref)
+
+
+@pytest.mark.parametrize("case", ROPE_CASES, ids=lambda c: c[0])
+def test_rope_and_cache_reference_golden(P, case):
+    """CUDA kernel vs the outputs of the reference's own RotaryEmbedding / rotate_half / scatter."""
+    name, dt, h, d, bs, nb, t, max_len, seed = case
+    gold = np.load(os.path.join(GOLD, "rope_cases.npz"))
+    qkv, positions, slots, k_cache, v_cache = make_rope_inputs(case)
+    assert tensor_sha(qkv, positions, slots, k_cache, v_cache) == str(gold[f"{name}/in_sha"]), "RNG drift"
+    cos, sin = (x.to(qkv.dtype) for x in O.rope_tables(d, max_len))
+    k_dev, v_dev = k_cache.to(DEV), v_cache.to(DEV)
+    q = P.rope_and_cache(qkv.to(DEV), positions.to(DEV), cos.to(DEV), sin.to(DEV), (k_dev, v_dev), slots.to(DEV), h)
+    assert torch.equal(q.float().cpu(), torch.from_numpy(gold[f"{name}/q"]))
+    assert torch.equal(k_dev.float().cpu(), torch.from_numpy(gold[f"{name}/k_cache"]))
+    assert torch.equal(v_dev.float().cpu(), torch.from_numpy(gold[f"{name}/v_cache"]))

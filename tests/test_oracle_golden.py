@@ -12,14 +12,15 @@ import numpy as np
 import pytest
 import torch
 
-from cases import (DECODE_CASES, PREFILL_CASES, make_decode_inputs, make_prefill_inputs,
-                   tensor_sha)
+from cases import (DECODE_CASES, PREFILL_CASES, ROPE_CASES, make_decode_inputs, make_prefill_inputs,
+                   make_rope_inputs, tensor_sha)
 from oracle import paged_attention_oracle as O
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 DEC = np.load(os.path.join(GOLD, "decode_cases.npz"))
 PRE = np.load(os.path.join(GOLD, "prefill_cases.npz"))
 INTS = json.load(open(os.path.join(GOLD, "integer_cases.json")))
+ROPE = np.load(os.path.join(GOLD, "rope_cases.npz"))
 
 
 # ---- integer contracts -----------------------------------------------------
@@ -178,3 +179,16 @@ def test_reshape_and_cache_bshd_and_block_ops():
     host = torch.zeros(3, bs, h, d)
     O.swap_blocks(kc, host, [(5, 1), (1, 0)], block_dim=0)
     assert torch.equal(host[1], kc[5]) and torch.equal(host[0], kc[1])
+
+
+# ---- RoPE + QKV split + KV scatter (engine steps 1b-3) ------------------------------------
+@pytest.mark.parametrize("case", ROPE_CASES, ids=lambda c: c[0])
+def test_rope_oracle_vs_reference_golden(case):
+    name, dt, h, d, bs, nb, t, max_len, seed = case
+    qkv, positions, slots, k_cache, v_cache = make_rope_inputs(case)
+    assert tensor_sha(qkv, positions, slots, k_cache, v_cache) == str(ROPE[f"{name}/in_sha"]), "RNG drift"
+    cos, sin = (x.to(qkv.dtype) for x in O.rope_tables(d, max_len))
+    q = O.rope_split_and_cache_bshd(qkv, positions, cos, sin, k_cache, v_cache, slots, h, h)
+    assert torch.equal(q.float(), torch.from_numpy(ROPE[f"{name}/q"]))              # bit-exact
+    assert torch.equal(k_cache.float(), torch.from_numpy(ROPE[f"{name}/k_cache"]))
+    assert torch.equal(v_cache.float(), torch.from_numpy(ROPE[f"{name}/v_cache"]))

@@ -45,6 +45,8 @@ SIGNATURES = {
     "pa_slot_mapping": (c_int, [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
     "pa_reshape_and_cache": (c_int, [c_void_p, c_void_p, c_int64, c_int64, POINTER(PaKvCache), c_void_p,
                                      c_int32, c_void_p]),
+    "pa_rope_and_cache": (c_int, [c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int64, c_int32, c_void_p,
+                                  c_void_p, c_int32, c_void_p, c_int64, c_int64, POINTER(PaKvCache), c_void_p]),
     "pa_copy_blocks": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_int64, c_void_p, c_int32, c_void_p]),
     "pa_swap_blocks": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int32, c_int64,
                                c_void_p, c_int32, c_int32, c_void_p]),

@@ -14,8 +14,10 @@ What is replaced (reference lines, relative to 05_mini_vllm/mini_vllm.py):
     slot 0 only and ignores the block table (acknowledged in its comments, :462-471), and its
     prefill branch ignores earlier chunks of a chunked prefill (:437-458).  Here every query token
     attends causally over its request's whole history, read THROUGH the block table:
-    decode tokens -> one ``paged_attention_decode_batched`` launch for all decode requests of the
-    step, prefill chunks -> ``paged_attention_prefill_chunk``.
+    on tensor-core shapes (bf16, block_size 16, head_dim 64 / 128) the whole mixed step - prefill
+    chunks and decode tokens - is ONE ``paged_attention_prefill_varlen`` launch; otherwise decode
+    tokens -> one ``paged_attention_decode_batched`` launch for all decode requests of the step,
+    prefill chunks -> ``paged_attention_prefill_chunk``.
 What is kept: QKV projection, RoPE, output projection (the module's own weights and ``rope``),
 ``Scheduler``, ``BlockAllocator``, ``Sampler``, ``MiniTransformer`` - untouched.
 
@@ -50,6 +52,12 @@ class StepMetadata:
     decode_block_tables: Optional[torch.Tensor] = None       # int32 [Bd, max_blocks]
     decode_ctx_lens: Optional[torch.Tensor] = None           # int32 [Bd] = position + 1
     prefill_chunks: List[tuple] = field(default_factory=list)   # (token offset, n, start_pos, int32 block table)
+    # varlen form of the WHOLE step (prefill chunks and decode tokens alike) for the one-launch
+    # tensor-core path: request i owns tokens [cu_q_lens[i], cu_q_lens[i + 1]) ending at ctx_lens[i]
+    all_block_tables: Optional[torch.Tensor] = None          # int32 [B, max_blocks]
+    cu_q_lens: Optional[torch.Tensor] = None                 # int32 [B + 1]
+    ctx_lens: Optional[torch.Tensor] = None                  # int32 [B]
+    max_q_len: int = 0
 
 
 def _build_metadata(scheduled, device) -> StepMetadata:
@@ -81,6 +89,18 @@ def _build_metadata(scheduled, device) -> StepMetadata:
         md.decode_rows = torch.tensor(dec_rows, dtype=torch.int64).to(device)
         md.decode_block_tables = table.to(device)
         md.decode_ctx_lens = torch.tensor(dec_lens, dtype=torch.int32).to(device)
+    if md.num_tokens:
+        width = max(max(len(b) for b in md.block_tables), 1)
+        table = torch.zeros(len(md.block_tables), width, dtype=torch.int32)
+        for i, b in enumerate(md.block_tables):
+            table[i, :len(b)] = torch.tensor(b, dtype=torch.int32)
+        cu = [0]
+        for n in md.num_tokens:
+            cu.append(cu[-1] + n)
+        md.all_block_tables = table.to(device)
+        md.cu_q_lens = torch.tensor(cu, dtype=torch.int32).to(device)
+        md.ctx_lens = torch.tensor([s + n for s, n in zip(md.start_pos, md.num_tokens)], dtype=torch.int32).to(device)
+        md.max_q_len = max(md.num_tokens)
     return md
 
 
@@ -104,6 +124,14 @@ def _attention_forward(attn, engine, x, positions, kv_cache, slot_mapping, seq_l
     t = x.shape[0]
     h, d = attn.num_heads, attn.head_dim
 
+    k_cache, v_cache = kv_cache
+    cache = (k_cache, v_cache)
+    fused = getattr(ops, "rope_and_cache", None)
+    if fused is not None and hasattr(attn.rope, "cos_cached"):
+        # steps 1b-3 in one kernel: split, RoPE with the module's own tables, K / V slot write
+        q = fused(attn.qkv(x), positions, attn.rope.cos_cached, attn.rope.sin_cached, cache, slot_mapping, h)
+        return _attend(attn, ops, md, q, cache, t, h, d)
+
     # steps 1-2 of the reference forward, unchanged: QKV projection and RoPE (:408-419)
     q, k, v = attn.qkv(x).chunk(3, dim=-1)
     q, k, v = q.reshape(t, h, d), k.reshape(t, h, d), v.reshape(t, h, d)
@@ -114,11 +142,17 @@ def _attention_forward(attn, engine, x, positions, kv_cache, slot_mapping, seq_l
     v = v.contiguous()
 
     # step 3: KV slot write into the model's own [NB, BS, H, D] buffers (:421-427)
-    k_cache, v_cache = kv_cache
-    cache = (k_cache, v_cache)
     ops.reshape_and_cache(k, v, cache, slot_mapping)
+    return _attend(attn, ops, md, q, cache, t, h, d)
 
+
+def _attend(attn, ops, md: StepMetadata, q, cache, t, h, d):
     # step 4: attention through the block tables
+    varlen = getattr(ops, "paged_attention_prefill_varlen", None)
+    if varlen is not None and ops.prefill_tensor_core_available(cache, h):
+        # tensor-core shapes: the whole mixed step (prefill chunks + decode tokens) in ONE launch
+        out = varlen(q, cache, md.all_block_tables, md.cu_q_lens, md.ctx_lens, md.max_q_len)
+        return attn.out_proj(out.reshape(t, h * d))
     out = torch.empty((t, h, d), dtype=q.dtype, device=q.device)
     if md.decode_rows is not None:
         q_dec = q.index_select(0, md.decode_rows)

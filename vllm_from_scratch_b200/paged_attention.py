@@ -252,6 +252,45 @@ def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, kv_cache: KvCacheA
     _lib.check(rc, "pa_reshape_and_cache")
 
 
+def rope_and_cache(qkv: torch.Tensor, positions: torch.Tensor, cos_cached: torch.Tensor, sin_cached: torch.Tensor,
+                   kv_cache: KvCacheArg, slot_mapping: torch.Tensor, num_q_heads: int,
+                   q_out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Fused RoPE + QKV split + KV slot write (mini_vllm.py:410-427 in one kernel).
+
+    qkv ``[T, (Hq + 2 Hkv) * D]`` straight from the QKV projection; ``cos_cached`` / ``sin_cached``
+    ``[max_len, D]`` are the reference ``RotaryEmbedding``'s own buffers.  Returns rotated Q
+    ``[T, Hq, D]``; rotated K and plain V land in their cache slots.  Bit-exact against the
+    reference's op-by-op torch evaluation in the same dtype."""
+    desc, kplane = _describe_cache(kv_cache)
+    for name, ten in (("qkv", qkv), ("positions", positions), ("cos_cached", cos_cached), ("sin_cached", sin_cached),
+                      ("slot_mapping", slot_mapping)):
+        _require_cuda(ten, name)
+    d, hkv = desc.head_dim, desc.num_kv_heads
+    if qkv.dim() != 2 or qkv.shape[1] != (num_q_heads + 2 * hkv) * d:
+        raise ValueError(f"qkv must be [T, {(num_q_heads + 2 * hkv) * d}]")
+    if not (qkv.dtype == cos_cached.dtype == sin_cached.dtype == kplane.dtype):
+        raise TypeError("qkv, the cos / sin tables and the cache must share one dtype")
+    if cos_cached.shape != sin_cached.shape or cos_cached.dim() != 2 or cos_cached.shape[1] != d:
+        raise ValueError("cos_cached / sin_cached must be [max_len, D]")
+    t = qkv.shape[0]
+    if positions.numel() != t or slot_mapping.numel() != t:
+        raise ValueError("positions and slot_mapping must have one entry per token")
+    if qkv.stride(1) != 1:
+        qkv = qkv.contiguous()
+    cos_cached, sin_cached = cos_cached.contiguous(), sin_cached.contiguous()
+    if q_out is None:
+        q_out = torch.empty((t, num_q_heads, d), dtype=qkv.dtype, device=qkv.device)
+    pos = positions.to(torch.int64).contiguous()
+    slots = slot_mapping.to(torch.int64).contiguous()
+    with _DeviceOf(kplane):
+        rc = _lib.load().pa_rope_and_cache(qkv.data_ptr(), qkv.stride(0), num_q_heads, cos_cached.data_ptr(),
+                                           sin_cached.data_ptr(), cos_cached.stride(0), cos_cached.shape[0],
+                                           pos.data_ptr(), slots.data_ptr(), t, q_out.data_ptr(), q_out.stride(0),
+                                           q_out.stride(1), ctypes.byref(desc), _stream_ptr())
+    _lib.check(rc, "pa_rope_and_cache")
+    return q_out
+
+
 # ---------------------------------------------------------------------------------------
 # decode
 # ---------------------------------------------------------------------------------------
