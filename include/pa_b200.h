@@ -208,8 +208,9 @@ int pa_prefill_varlen(const void* q, int64_t q_stride_t, int64_t q_stride_h,
 /* 1 when pa_prefill / pa_prefill_varlen take the tensor-core path for this
  * cache and head count (pointer alignment is checked per call), else 0.       */
 int pa_prefill_tc_available(const PaKvCache* cache, int32_t num_q_heads);
-/* 0 = automatic (default); 1 = force the decode-kernel formulation in
- * pa_prefill even where the tensor-core kernel applies.  Returns the old value. */
+/* 0 = automatic (default: the two-tile ping-pong tcgen05 kernel); 1 = force the
+ * decode-kernel formulation in pa_prefill even where a tensor-core kernel
+ * applies; 2 = the one-tile-per-CTA tcgen05 kernel.  Returns the old value.     */
 int pa_prefill_force_path(int path);
 
 /* ---- test / tuning hook ---------------------------------------------------

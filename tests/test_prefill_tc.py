@@ -28,6 +28,15 @@ def lib():
     return _lib.load()
 
 
+@pytest.fixture(autouse=True, params=[0, 2], ids=["pingpong", "onetile"])
+def tc_kernel(request, lib):
+    """Every test runs through both tcgen05 kernels: the two-tile ping-pong one (default) and the
+    one-tile-per-CTA one (pa_prefill_force_path(2))."""
+    old = lib.pa_prefill_force_path(request.param)
+    yield request.param
+    lib.pa_prefill_force_path(old)
+
+
 def _make_seq(g, total, hq, hkv, d, bs, nb, poison=False):
     """One sequence of `total` tokens scattered over a pool of nb blocks."""
     q = torch.randn(total, hq, d, generator=g).to(torch.bfloat16)
@@ -77,11 +86,11 @@ def test_prefill_tc_matches_decode_formulation(P, lib):
     kv_dev, q_dev = kv.to(DEV), q.to(DEV)
     bt_dev = torch.tensor(bt, dtype=torch.int32, device=DEV)
     tc = P.paged_attention_prefill_chunk(q_dev[100:], kv_dev, bt_dev, 100)
-    old = lib.pa_prefill_force_path(1)
+    cur = lib.pa_prefill_force_path(1)
     try:
         dec = P.paged_attention_prefill_chunk(q_dev[100:], kv_dev, bt_dev, 100)
     finally:
-        lib.pa_prefill_force_path(old)
+        lib.pa_prefill_force_path(cur)
     assert (tc.float() - dec.float()).abs().max().item() <= TOL
     again = P.paged_attention_prefill_chunk(q_dev[100:], kv_dev, bt_dev, 100)
     assert torch.equal(tc, again)                     # bit-reproducible

@@ -303,7 +303,8 @@ extern "C" int pa_prefill_varlen(const void* q, int64_t q_stride_t, int64_t q_st
   p.cu_q_lens = cu_q_lens; p.ctx_lens = ctx_lens;
   p.batch = batch; p.max_q_len = max_q_len;
   if (!pa_prefill_tc_supported(p, cache->dtype, cache->block_size)) return PA_ERR_UNSUPPORTED;
-  return pa_launch_prefill_tc(p, static_cast<cudaStream_t>(stream));
+  return g_prefill_force.load() == 2 ? pa_launch_prefill_tc(p, static_cast<cudaStream_t>(stream))
+                                     : pa_launch_prefill_tc2(p, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t o_stride_t,
@@ -324,7 +325,8 @@ extern "C" int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
       tp.ctx_len_single = start_pos + num_tokens;
       if (pa_prefill_tc_supported(tp, cache->dtype, cache->block_size)) {
         if (sm_count() <= 0) return PA_ERR_NO_DEVICE;
-        return pa_launch_prefill_tc(tp, static_cast<cudaStream_t>(stream));
+        return g_prefill_force.load() == 2 ? pa_launch_prefill_tc(tp, static_cast<cudaStream_t>(stream))
+                                           : pa_launch_prefill_tc2(tp, static_cast<cudaStream_t>(stream));
       }
     }
   }

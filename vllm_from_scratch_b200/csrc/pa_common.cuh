@@ -168,6 +168,8 @@ struct PaPrefillParams {
   int32_t num_q_heads, num_kv_heads, head_dim, group;
   int32_t pos_head;       // which of tensor-map dims 3 / 4 is the head axis
   float scale_log2e;
+  int32_t debug;          // bring-up knob (env PA_PREFILL_DEBUG): 0 = normal; see pa_prefill_tc2.cu
 };
 bool pa_prefill_tc_supported(const PaPrefillParams& p, int dtype, int block_size);
-int pa_launch_prefill_tc(const PaPrefillParams& p, cudaStream_t stream);
+int pa_launch_prefill_tc(const PaPrefillParams& p, cudaStream_t stream);    // one 128-row tile per CTA
+int pa_launch_prefill_tc2(const PaPrefillParams& p, cudaStream_t stream);   // two tiles per CTA, ping-pong

@@ -1,0 +1,420 @@
+// Paged prefill / chunked-prefill attention, tcgen05 + TMEM, ping-pong version: TWO 128-row query
+// tiles per CTA, each with its own softmax warpgroup, sharing every K / V tile; P stays in TMEM.
+//
+// Same contract as pa_prefill_tc.cu (reference: 01_paged_attention/paged_attention.py:125-136,
+// 05_mini_vllm/mini_vllm.py:437-458; varlen batches of query chunks that attend causally to
+// their whole paged history).  Why this shape (measurements: tools/umma_bench.cu and
+// profiles/r01_prefill_*):
+//   * a tcgen05.mma whose A operand is in SHARED memory costs >= 90.6 cycles on B200 whatever N is
+//     (the 128 x 16 A slice is re-read every instruction); the math floor is 128 * N / 256 cycles,
+//     so SS MMAs run at 70 % of peak for N = 128 and 35 % for N = 64.  Hence 128-key tiles for
+//     S = Q K^T (SS, 90 cycles / instruction), and O += P V with P as the A operand IN TMEM (TS,
+//     64 cycles / instruction at N = D = 128): 8 x 90 + 8 x 64 cycles per (tile, 128 keys)
+//     against 8 x 64 + 8 x 64 of pure math - an 83 % ceiling.
+//   * one softmax warpgroup cannot keep the pipe fed (pa_prefill_tc.cu: tensor pipe 29 % active):
+//     a CTA owns rows [0,128) = tile A and [128,256) = tile B of one (sequence, KV head)
+//     (2 * R tokens x g heads, R = 128 / g); warps 0-3 are A's softmax warpgroup, 4-7 B's
+//     (warp % 4 = TMEM lane quarter), warp 8 the TMA producer, warp 9 the MMA issuer.  While A's
+//     warpgroup exponentiates, the pipe runs B's P V and the next Q_B K^T, and vice versa.
+//   * bf16 P overwrites the first 64 columns of its own S tile (tcgen05.st), so S is single-
+//     buffered: the issuer queues PV_w(t) and then QK_w(t + 1), which the pipe executes in order.
+//   * K / V tiles are 128 keys x D (32 KiB) in a 5-slot ring (K0 V0 K1 V1 ...), gathered by TMA
+//     through the block table, slab-major so a whole tile is one canonical UMMA operand.
+//   * softmax per thread = one row of 128 scores: one tcgen05.ld pass, FMNMX3 row max, FFMA2 /
+//     ex2 / FADD2 (packed fp32x2), bf16 pack.  The O accumulator is rescaled only when a row's
+//     maximum grew by more than 2^8 over the maximum in use (exact: l and O share that reference).
+// TMEM (512 columns): S_A / P_A [0,128) | S_B / P_B [128,256) | O_A [256,384) | O_B [384,512).
+// Shared memory (D = 128): Q_A, Q_B 32 KiB each | ring 5 x 32 KiB = 224 KiB.
+#include <cuda.h>
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "pa_common.cuh"
+#include "pa_tc_common.cuh"
+
+int pa_get_kv_tensor_map(const void* base, const PaDecodeParams& p, int box_halves, CUtensorMap* out, int* pos_head);
+
+namespace {
+
+constexpr int kBS = 16;
+constexpr int kTileN = 128;                   // keys per KV tile
+constexpr int kBlocksPerTile = kTileN / kBS;  // 8
+constexpr int kWgThreads = 128;
+constexpr int kThreads = 384;                 // 2 softmax warpgroups + a third warpgroup: producer warp, MMA warp, 2 idle
+constexpr int kRing = 5;                      // K / V items in flight
+constexpr uint32_t kSlab = kRows * 128;       // [128 rows][128 B]: one 64-column slab of a Q, K or V tile
+constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kTmemO = 256;
+constexpr float kRescaleThreshold = 8.f;      // log2 units
+constexpr uint32_t FULL = 0xffffffffu;
+
+// Barrier slots (8 bytes each).  Per-warpgroup groups are indexed [wg].
+enum : int {
+  kBarKvFull = 0, kBarKvEmpty = kRing,
+  kBarSFull = 2 * kRing,            // [wg]  tcgen05.commit after Q_w K(t)^T (implies every earlier MMA is done)
+  kBarPReady = kBarSFull + 2,       // [wg]  128 softmax threads: P(t) is in TMEM, O is rescaled
+  kBarODone = kBarPReady + 2,       // [wg]  tcgen05.commit after the warpgroup's last P V
+  kBarQReady = kBarODone + 2,       // [wg]  128 softmax threads: the Q tile is in shared memory
+  kNumBars = kBarQReady + 2
+};
+
+// D[tmem] (+)= A[tmem] . B[smem]
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+
+
+template <int HD>
+__global__ void __launch_bounds__(kThreads, 1)
+pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
+                      const PaPrefillParams p) {
+  constexpr int HALVES = HD / 64;
+  constexpr uint32_t kItem = HALVES * kSlab;                 // one Q, K or V tile: [half][128 rows][128 B]
+
+  // ---- which work tile: 2 * R tokens of one (sequence, KV head) ----
+  const int s = blockIdx.z, h = blockIdx.y;
+  const int g = p.group, R = kRows / g;
+  int q_start, q_len, ctx;
+  if (p.cu_q_lens) {
+    q_start = __ldg(p.cu_q_lens + s);
+    q_len = __ldg(p.cu_q_lens + s + 1) - q_start;
+    ctx = __ldg(p.ctx_lens + s);
+  } else {
+    q_start = 0; q_len = p.num_tokens; ctx = p.ctx_len_single;
+  }
+  if (q_len <= 0 || ctx < q_len) return;                     // nothing to do / malformed: leave `out` alone
+  const int cta_tile = (int)gridDim.x - 1 - (int)blockIdx.x; // long tiles first
+  const int tok0 = cta_tile * 2 * R;
+  if (tok0 >= q_len) return;
+  const int ntok_cta = min(2 * R, q_len - tok0);
+  const int ntok_a = min(R, ntok_cta), ntok_b = ntok_cta - ntok_a;
+  const int pos0 = ctx - q_len + tok0;                       // smallest query position of the CTA
+  const int n_a = (pos0 + ntok_a - 1) / kTileN + 1;
+  const int n_b = ntok_b > 0 ? (pos0 + ntok_cta - 1) / kTileN + 1 : 0;
+  const int n = max(n_a, n_b);                               // KV tiles the CTA streams
+  const int nblk_need = (pos0 + ntok_cta - 1) / kBS + 1;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sQ = base;                                  // [2] tiles
+  const uint32_t sRing = sQ + 2 * kItem;
+  const uint32_t sBar = sRing + kRing * kItem;
+  const uint32_t sTmem = sBar + kNumBars * 8;
+  uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));     // generic pointer to `base`
+  auto bar = [&](int i) { return sBar + 8u * i; };
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (warp == 8 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_k) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_v) : "memory");
+    for (int i = 0; i < kNumBars; ++i) {
+      const bool by_warpgroup = (i >= kBarPReady && i < kBarODone) || i >= kBarQReady;
+      mbar_init(bar(i), by_warpgroup ? kWgThreads : 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 9) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sTmem), "n"(kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (sTmem - base));
+
+  if (warp < 8) {
+    // =============================== softmax warpgroups ===============================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");    // 2 x 128 x 232 + 128 x 40 registers <= 64 K
+    const int w = warp >> 2;                                 // 0 = tile A, 1 = tile B
+    const int wt = tid & (kWgThreads - 1);                   // row within the tile = TMEM lane
+    const int ntok_w = w == 0 ? ntok_a : ntok_b;
+    const int n_w = w == 0 ? n_a : n_b;
+    if (ntok_w > 0) {
+      const int tokw0 = tok0 + w * R, posw0 = pos0 + w * R;
+      // ---- Q tile -> shared memory, K-major, 128-byte swizzle (row = (token, head-in-group)) ----
+      {
+        const __nv_bfloat16* qb = static_cast<const __nv_bfloat16*>(p.q);
+        constexpr int CH = HD / 8;                           // 16-byte chunks per row
+        uint8_t* qdst = gen + (sQ - base) + (uint32_t)w * kItem;
+        for (int idx = wt; idx < kRows * CH; idx += kWgThreads) {
+          const int row = idx / CH, c = idx % CH;
+          const int ti = row / g, j = row - ti * g;
+          uint4 val = make_uint4(0, 0, 0, 0);
+          if (ti < ntok_w)
+            val = __ldg(reinterpret_cast<const uint4*>(qb + (int64_t)(q_start + tokw0 + ti) * p.q_stride_t +
+                                                       (int64_t)(h * g + j) * p.q_stride_h + c * 8));
+          const uint32_t off = (uint32_t)(c >> 3) * kSlab + (uint32_t)row * 128u + (uint32_t)(((c & 7) ^ (row & 7)) << 4);
+          *reinterpret_cast<uint4*>(qdst + off) = val;
+        }
+        fence_proxy_async();
+        mbar_arrive(bar(kBarQReady + w));
+      }
+      const int ti = wt / g, j = wt - ti * g;
+      const bool valid = ti < ntok_w;
+      const int qpos = posw0 + min(ti, ntok_w - 1);
+      const float scale = p.scale_log2e;
+      const uint64_t scale2 = pack2(scale, scale);
+      const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+      const uint32_t tS = lane_base + (uint32_t)w * 128u, tO = lane_base + kTmemO + (uint32_t)w * 128u;
+      float m_used = -INFINITY, l = 0.f;
+
+      for (int t = 0; t < n_w; ++t) {
+        uint32_t v[kTileN];
+        // S(t) complete; the commit behind this barrier also covers P V(t - 1): O holds tiles < t
+        mbar_wait(bar(kBarSFull + w), t & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int cc = 0; cc < kTileN / 32; ++cc) tmem_ld32(tS + cc * 32, v + cc * 32);
+        tmem_wait_ld();
+
+        const int kbase = t * kTileN;
+        if (kbase + kTileN - 1 > posw0) {                    // causal / ragged mask (warpgroup-uniform test)
+#pragma unroll
+          for (int c = 0; c < kTileN; ++c)
+            if (kbase + c > qpos) v[c] = 0xff800000u;        // -inf, also replaces NaN from stale keys
+        }
+        float mx = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < kTileN; c += 2) mx = fmax3(mx, __uint_as_float(v[c]), __uint_as_float(v[c + 1]));
+        const float ms = mx * scale;
+        // Lazy rescale: keep exponentiating against the maximum in use until the true maximum has
+        // grown by more than 2^8; p <= 256 then, and l / O use the same reference point.
+        const bool grow = ms > m_used + kRescaleThreshold;   // always true at t == 0 (key 0 is visible)
+        float alpha = 1.f;
+        if (grow) {
+          alpha = fast_exp2(m_used - ms);
+          m_used = ms;
+        }
+        if (t > 0 && __any_sync(FULL, grow)) {               // rescale O before P V(t) accumulates into it
+#pragma unroll
+          for (int cc = 0; cc < HD / 32; ++cc) {
+            uint32_t o[32];
+            tmem_ld32(tO + cc * 32, o);
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st32(tO + cc * 32, o);
+          }
+        }
+        const uint64_t negm2 = pack2(-m_used, -m_used);
+        uint64_t sum2 = pack2(0.f, 0.f);
+        // exponentiate in place: v[c] <- bf16x2(p[2c], p[2c + 1]) for c < 64; P = first 64 columns of S
+#pragma unroll
+        for (int c = 0; c < kTileN / 2; ++c) {
+          float x0, x1;
+          unpack2(ffma2(pack2(__uint_as_float(v[2 * c]), __uint_as_float(v[2 * c + 1])), scale2, negm2), x0, x1);
+          const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+          sum2 = fadd2(sum2, pack2(p0, p1));
+          v[c] = pack_bf16(p0, p1);
+          if ((c & 31) == 31) tmem_st32(tS + (c - 31), v + (c - 31));
+        }
+        float s0, s1;
+        unpack2(sum2, s0, s1);
+        l = l * alpha + (s0 + s1);
+        // ---- the CTA's last tile: V rows that were not loaded or lie beyond the context must be finite ----
+        if (t == n - 1) {
+          const int zero_from = min(nblk_need * kBS, ctx) - kbase;
+          if (zero_from < kTileN) {
+            const int item = 2 * t + 1;
+            mbar_wait(bar(kBarKvFull + item % kRing), (item / kRing) & 1);
+            const int nz = (kTileN - zero_from) * HALVES * 8;
+            uint8_t* vb = gen + (sRing - base) + (uint32_t)(item % kRing) * kItem;
+            for (int idx = wt; idx < nz; idx += kWgThreads) {
+              const int row = zero_from + idx / (HALVES * 8), rem = idx % (HALVES * 8);
+              *reinterpret_cast<uint4*>(vb + (uint32_t)(rem >> 3) * kSlab + (uint32_t)row * 128u + (uint32_t)((rem & 7) << 4)) =
+                  make_uint4(0, 0, 0, 0);
+            }
+            fence_proxy_async();
+          }
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(bar(kBarPReady + w));
+      }
+
+      // ---- epilogue: O / l -> out ----
+      mbar_wait(bar(kBarODone + w), 0);
+      tc_fence_after();
+      const float inv = 1.f / l;
+      __nv_bfloat16* ob = static_cast<__nv_bfloat16*>(p.out) + (int64_t)(q_start + tokw0 + ti) * p.o_stride_t +
+                          (int64_t)(h * g + j) * p.o_stride_h;
+#pragma unroll
+      for (int cc = 0; cc < HD / 32; ++cc) {
+        uint32_t o[32];
+        tmem_ld32(tO + cc * 32, o);
+        tmem_wait_ld();
+        if (valid) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint4 wv;
+            wv.x = pack_bf16(__uint_as_float(o[8 * i]) * inv, __uint_as_float(o[8 * i + 1]) * inv);
+            wv.y = pack_bf16(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv);
+            wv.z = pack_bf16(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv);
+            wv.w = pack_bf16(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv);
+            *reinterpret_cast<uint4*>(ob + cc * 32 + i * 8) = wv;
+          }
+        }
+      }
+      tc_fence_before();
+    }
+  }
+  else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+  if (warp == 8) {
+    // =============================== TMA producer ===============================
+    const int32_t* bt = p.block_tables + (int64_t)s * p.bt_stride;
+    const int b = lane / HALVES, hf = lane % HALVES;
+    for (int t = 0; t < n; ++t) {
+      const int blk0 = t * kBlocksPerTile;
+      const int nb = min(kBlocksPerTile, nblk_need - blk0);
+      const bool mine = lane < kBlocksPerTile * HALVES && b < nb;
+      int blk = 0;
+      if (mine) blk = __ldg(bt + blk0 + b);
+      const int c3 = p.pos_head == 3 ? h : blk, c4 = p.pos_head == 3 ? blk : h;
+      const uint32_t in_item = (uint32_t)hf * kSlab + (uint32_t)b * (kBS * 128);
+#pragma unroll
+      for (int kv = 0; kv < 2; ++kv) {                       // item 2t = K(t), item 2t + 1 = V(t)
+        const int item = 2 * t + kv, slot = item % kRing;
+        mbar_wait(bar(kBarKvEmpty + slot), ((item / kRing) & 1) ^ 1);
+        if (lane == 0) mbar_expect_tx(bar(kBarKvFull + slot), (uint32_t)nb * HALVES * kBS * 128);
+        __syncwarp();
+        if (mine) tma_load_half(sRing + (uint32_t)slot * kItem + in_item, kv ? &tm_v : &tm_k, bar(kBarKvFull + slot), hf, c3, c4);
+      }
+    }
+  } else if (warp == 9) {
+    // =============================== MMA issuer ===============================
+    constexpr uint32_t idesc_s = umma_idesc(kTileN, false);
+    constexpr uint32_t idesc_o = umma_idesc(HD, true);
+    auto wait_item = [&](int item) { mbar_wait(bar(kBarKvFull + item % kRing), (item / kRing) & 1); };
+    auto free_item = [&](int item) {
+      if (lane == 0) umma_commit(bar(kBarKvEmpty + item % kRing));
+      __syncwarp();
+    };
+    auto qk = [&](int w, int t) {                            // S_w = Q_w K(t)^T   (both operands in shared memory)
+      if (lane == 0) {
+        const uint32_t a0 = sQ + (uint32_t)w * kItem, b0 = sRing + (uint32_t)((2 * t) % kRing) * kItem;
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const uint32_t koff = (uint32_t)(kk >> 2) * kSlab + (uint32_t)(kk & 3) * 32u;
+          umma_bf16(tmem + (uint32_t)w * 128u, umma_desc(a0 + koff, 16, 1024), umma_desc(b0 + koff, 16, 1024), idesc_s, kk > 0);
+        }
+        umma_commit(bar(kBarSFull + w));
+      }
+      __syncwarp();
+    };
+    auto pv = [&](int w, int t, bool last) {                 // O_w += P_w V(t)      (P in TMEM, V in shared memory)
+      mbar_wait(bar(kBarPReady + w), t & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t b0 = sRing + (uint32_t)((2 * t + 1) % kRing) * kItem;
+#pragma unroll
+        for (int ks = 0; ks < kTileN / 16; ++ks)
+          umma_bf16_ts(tmem + kTmemO + (uint32_t)w * 128u, tmem + (uint32_t)w * 128u + (uint32_t)ks * 8u,
+                       umma_desc(b0 + (uint32_t)ks * (16 * 128), kSlab, 1024), idesc_o, (t > 0 || ks > 0) ? 1u : 0u);
+        if (last) umma_commit(bar(kBarODone + w));
+      }
+      __syncwarp();
+    };
+    mbar_wait(bar(kBarQReady), 0);
+    if (ntok_b > 0) mbar_wait(bar(kBarQReady + 1), 0);
+    tc_fence_after();
+    wait_item(0);
+    qk(0, 0);
+    if (n_b > 0) qk(1, 0);
+    free_item(0);
+    for (int t = 0; t < n; ++t) {
+      wait_item(2 * t + 1);                                  // V(t)
+      if (t + 1 < n) wait_item(2 * t + 2);                   // K(t + 1)
+      if (t < n_a) {
+        pv(0, t, t == n_a - 1);
+        if (t + 1 < n_a) qk(0, t + 1);
+      }
+      if (t < n_b) {
+        pv(1, t, t == n_b - 1);
+        if (t + 1 < n_b) qk(1, t + 1);
+      }
+      free_item(2 * t + 1);
+      if (t + 1 < n) free_item(2 * t + 2);
+    }
+    tc_fence_before();
+  }
+  }
+
+  __syncthreads();
+  if (warp == 9) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kTmemCols) : "memory");
+  }
+}
+
+template <int HD>
+constexpr size_t smem_bytes() {
+  return 1024 + (size_t)(HD / 64) * kSlab * (2 + kRing) + kNumBars * 8 + 16;
+}
+
+template <int HD>
+int launch(const PaPrefillParams& p, const CUtensorMap& mk, const CUtensorMap& mv, cudaStream_t stream) {
+  auto kern = pa_prefill_tc2_kernel<HD>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes<HD>()) != cudaSuccess)
+      return -5;
+    attr_set = true;
+  }
+  const int R2 = 2 * (kRows / p.group);
+  dim3 grid((p.max_q_len + R2 - 1) / R2, p.num_kv_heads, p.batch);
+  kern<<<grid, kThreads, smem_bytes<HD>(), stream>>>(mk, mv, p);
+  return cudaGetLastError() == cudaSuccess ? 0 : -5;
+}
+
+}  // namespace
+
+int pa_launch_prefill_tc2(const PaPrefillParams& p_in, cudaStream_t stream) {
+  PaPrefillParams p = p_in;
+  PaDecodeParams kv;
+  memset(&kv, 0, sizeof(kv));
+  kv.k = p.k; kv.v = p.v;
+  kv.kv_stride_block = p.kv_stride_block; kv.kv_stride_head = p.kv_stride_head; kv.kv_stride_slot = p.kv_stride_slot;
+  kv.num_kv_heads = p.num_kv_heads; kv.head_dim = p.head_dim;
+  CUtensorMap mk, mv;
+  int ph = 3;
+  int rc = pa_get_kv_tensor_map(p.k, kv, 1, &mk, &ph);
+  if (rc) return rc;
+  rc = pa_get_kv_tensor_map(p.v, kv, 1, &mv, &ph);
+  if (rc) return rc;
+  p.pos_head = ph;
+  return p.head_dim == 128 ? launch<128>(p, mk, mv, stream) : launch<64>(p, mk, mv, stream);
+}
