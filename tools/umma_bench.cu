@@ -16,7 +16,19 @@ struct Cfg {
   int b_mn_major;   // 0: B K-major (QK^T style), 1: B MN-major (PV style)
   int a_step;       // bytes added to the A descriptor start per instruction (cycled over 4)
   int distinct;     // 1: cycle through 8 different operand offsets, 0: same operands every time
+  int a_tmem;       // 1: A operand in tensor memory (TS), 0: in shared memory (SS)
+  int alt;          // 1: alternate SS (N = 128, K-major B) and TS (MN-major B) instructions, as the prefill kernel does
 };
+
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 
 __global__ void __launch_bounds__(128, 1) umma_bench_kernel(Cfg c, int iters, long long* out) {
   extern __shared__ uint8_t smem_raw[];
@@ -40,16 +52,37 @@ __global__ void __launch_bounds__(128, 1) umma_bench_kernel(Cfg c, int iters, lo
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = tmem_slot;
-  if (warp == 1 && lane == 0) {
+  if (warp == 1 && elect_one()) {
+    // descriptors are precomputed and the loop is unrolled by 8: the issuing thread must not be the limit
     const uint32_t idesc = umma_idesc(c.n, c.b_mn_major != 0);
+    const uint32_t idesc_ss = umma_idesc(128, false), idesc_ts = umma_idesc(128, true);
     const uint32_t sA = base, sB = base + 64 * 1024;
+    uint64_t da[8], db[8], dbk[8], dbm[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      da[j] = umma_desc(sA + (uint32_t)(j >> 2) * 16384u + (uint32_t)(j & 3) * 32u, 16, 1024);
+      dbk[j] = umma_desc(sB + (uint32_t)(j >> 2) * 16384u + (uint32_t)(j & 3) * 32u, 16, 1024);
+      dbm[j] = umma_desc(sB + (uint32_t)j * 2048u, 16384, 1024);
+      db[j] = c.b_mn_major ? dbm[j] : dbk[j];
+    }
     long long t0 = clock64();
-    for (int i = 0; i < iters; ++i) {
-      const int j = c.distinct ? (i & 7) : 0;
-      const uint64_t da = umma_desc(sA + (uint32_t)(j >> 2) * 16384u + (uint32_t)(j & 3) * c.a_step, 16, 1024);
-      const uint64_t db = c.b_mn_major ? umma_desc(sB + (uint32_t)j * 2048u, 16384, 1024)
-                                       : umma_desc(sB + (uint32_t)(j >> 2) * 16384u + (uint32_t)(j & 3) * 32u, 16, 1024);
-      umma_bf16(tmem, da, db, idesc, 1);
+    if (c.alt) {
+      for (int i = 0; i < iters; i += 16) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) umma_bf16(tmem, da[j], dbk[j], idesc_ss, 1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) umma_bf16_ts(tmem + 256, tmem + 128 + (uint32_t)j * 8u, dbm[j], idesc_ts, 1);
+      }
+    } else if (c.a_tmem) {
+      for (int i = 0; i < iters; i += 8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) umma_bf16_ts(tmem, tmem + 256 + (uint32_t)j * 8u, db[j], idesc, 1);
+      }
+    } else {
+      for (int i = 0; i < iters; i += 8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) umma_bf16(tmem, da[j], db[j], idesc, 1);
+      }
     }
     umma_commit(smem_u32(&barv));
     mbar_wait(smem_u32(&barv), 0);
@@ -67,12 +100,13 @@ int main() {
   cudaMalloc(&d_out, 8);
   cudaFuncSetAttribute(umma_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   const Cfg cfgs[] = {
-      {128, 0, 32, 1}, {128, 0, 32, 0}, {64, 0, 32, 1}, {256, 0, 32, 1}, {16, 0, 32, 1}, {32, 0, 32, 1},
-      {128, 1, 32, 1}, {128, 1, 32, 0}, {64, 1, 32, 1}, {256, 1, 32, 1},
+      {128, 0, 32, 1, 0, 0}, {64, 0, 32, 1, 0, 0}, {32, 0, 32, 1, 0, 0}, {256, 0, 32, 1, 0, 0}, {128, 1, 32, 1, 0, 0}, {256, 1, 32, 1, 0, 0},
+      {128, 1, 32, 1, 1, 0}, {64, 1, 32, 1, 1, 0}, {32, 1, 32, 1, 1, 0}, {256, 1, 32, 1, 1, 0}, {128, 0, 32, 1, 1, 0}, {64, 0, 32, 1, 1, 0},
+      {128, 0, 32, 1, 0, 1},
   };
   const int iters = 4096;
   for (const Cfg& c : cfgs) {
-    for (int grid : {1, 148}) {
+    for (int grid : {148}) {
       long long h = 0;
       for (int rep = 0; rep < 2; ++rep) {
         umma_bench_kernel<<<grid, 128, 200 * 1024>>>(c, iters, d_out);
@@ -81,7 +115,7 @@ int main() {
       }
       cudaMemcpy(&h, d_out, 8, cudaMemcpyDeviceToHost);
       const double cyc = (double)h / iters;
-      printf("N=%3d B=%s distinct=%d grid=%3d : %.1f cycles/MMA  (floor %d)  -> %.0f flop/clk/SM\n", c.n,
+      printf("%s N=%3d B=%s distinct=%d grid=%3d : %.1f cycles/MMA  (floor %d)  -> %.0f flop/clk/SM\n", c.alt ? "SS/TS alternating" : (c.a_tmem ? "TS" : "SS"), c.n,
              c.b_mn_major ? "MN" : "K ", c.distinct, grid, cyc, 128 * c.n / 256, 2.0 * 128 * c.n * 16 / cyc);
     }
   }

@@ -168,7 +168,8 @@ struct PaPrefillParams {
   int32_t num_q_heads, num_kv_heads, head_dim, group;
   int32_t pos_head;       // which of tensor-map dims 3 / 4 is the head axis
   float scale_log2e;
-  int32_t debug;          // bring-up knob (env PA_PREFILL_DEBUG): 0 = normal; see pa_prefill_tc2.cu
+  int32_t debug;          // bring-up knob, 0 = normal
+  long long* trace;       // PA_PREFILL_TRACE=1: per-tile clock64 stamps of CTA (0,0,0), else null
 };
 bool pa_prefill_tc_supported(const PaPrefillParams& p, int dtype, int block_size);
 int pa_launch_prefill_tc(const PaPrefillParams& p, cudaStream_t stream);    // one 128-row tile per CTA

@@ -27,6 +27,7 @@
 // Shared memory (D = 128): Q_A, Q_B 32 KiB each | ring 5 x 32 KiB = 224 KiB.
 #include <cuda.h>
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -53,8 +54,8 @@ constexpr uint32_t FULL = 0xffffffffu;
 enum : int {
   kBarKvFull = 0, kBarKvEmpty = kRing,
   kBarSFull = 2 * kRing,            // [wg]  tcgen05.commit after Q_w K(t)^T (implies every earlier MMA is done)
-  kBarPReady = kBarSFull + 2,       // [wg]  128 softmax threads: P(t) is in TMEM, O is rescaled
-  kBarODone = kBarPReady + 2,       // [wg]  tcgen05.commit after the warpgroup's last P V
+  kBarPReady = kBarSFull + 2,       // [wg][2]  128 softmax threads: keys [0,64) / [64,128) of P(t) are in TMEM (and O is rescaled)
+  kBarODone = kBarPReady + 4,       // [wg]  tcgen05.commit after the warpgroup's last P V
   kBarQReady = kBarODone + 2,       // [wg]  128 softmax threads: the Q tile is in shared memory
   kNumBars = kBarQReady + 2
 };
@@ -94,6 +95,12 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
   return r;
 }
 
+
+constexpr int kTraceTiles = 48, kTraceSlots = 16;
+#define PA_TRACE(slot, t)                                                                         \
+  do {                                                                                            \
+    if (trace_on && (t) < kTraceTiles) p.trace[(t) * kTraceSlots + (slot)] = clock64();           \
+  } while (0)
 
 template <int HD>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -135,6 +142,7 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
   auto bar = [&](int i) { return sBar + 8u * i; };
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool trace_on = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (tid & 127) == 0;
 
   if (warp == 8 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_k) : "memory");
@@ -157,7 +165,7 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
 
   if (warp < 8) {
     // =============================== softmax warpgroups ===============================
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");    // 2 x 128 x 232 + 128 x 40 registers <= 64 K
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");    // from 168: the 128 x 128 registers the third warpgroup gives up cover 64 x 256
     const int w = warp >> 2;                                 // 0 = tile A, 1 = tile B
     const int wt = tid & (kWgThreads - 1);                   // row within the tile = TMEM lane
     const int ntok_w = w == 0 ? ntok_a : ntok_b;
@@ -195,10 +203,12 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
         uint32_t v[kTileN];
         // S(t) complete; the commit behind this barrier also covers P V(t - 1): O holds tiles < t
         mbar_wait(bar(kBarSFull + w), t & 1);
+        PA_TRACE(5 * w + 0, t);
         tc_fence_after();
 #pragma unroll
         for (int cc = 0; cc < kTileN / 32; ++cc) tmem_ld32(tS + cc * 32, v + cc * 32);
         tmem_wait_ld();
+        PA_TRACE(5 * w + 1, t);
 
         const int kbase = t * kTileN;
         if (kbase + kTileN - 1 > posw0) {                    // causal / ragged mask (warpgroup-uniform test)
@@ -206,10 +216,13 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
           for (int c = 0; c < kTileN; ++c)
             if (kbase + c > qpos) v[c] = 0xff800000u;        // -inf, also replaces NaN from stale keys
         }
-        float mx = -INFINITY;
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};     // 4 independent FMNMX3 chains
 #pragma unroll
-        for (int c = 0; c < kTileN; c += 2) mx = fmax3(mx, __uint_as_float(v[c]), __uint_as_float(v[c + 1]));
-        const float ms = mx * scale;
+        for (int c = 0; c < kTileN; c += 8) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) mx4[i] = fmax3(mx4[i], __uint_as_float(v[c + 2 * i]), __uint_as_float(v[c + 2 * i + 1]));
+        }
+        const float ms = fmaxf(fmax3(mx4[0], mx4[1], mx4[2]), mx4[3]) * scale;
         // Lazy rescale: keep exponentiating against the maximum in use until the true maximum has
         // grown by more than 2^8; p <= 256 then, and l / O use the same reference point.
         const bool grow = ms > m_used + kRescaleThreshold;   // always true at t == 0 (key 0 is visible)
@@ -229,21 +242,6 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
             tmem_st32(tO + cc * 32, o);
           }
         }
-        const uint64_t negm2 = pack2(-m_used, -m_used);
-        uint64_t sum2 = pack2(0.f, 0.f);
-        // exponentiate in place: v[c] <- bf16x2(p[2c], p[2c + 1]) for c < 64; P = first 64 columns of S
-#pragma unroll
-        for (int c = 0; c < kTileN / 2; ++c) {
-          float x0, x1;
-          unpack2(ffma2(pack2(__uint_as_float(v[2 * c]), __uint_as_float(v[2 * c + 1])), scale2, negm2), x0, x1);
-          const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
-          sum2 = fadd2(sum2, pack2(p0, p1));
-          v[c] = pack_bf16(p0, p1);
-          if ((c & 31) == 31) tmem_st32(tS + (c - 31), v + (c - 31));
-        }
-        float s0, s1;
-        unpack2(sum2, s0, s1);
-        l = l * alpha + (s0 + s1);
         // ---- the CTA's last tile: V rows that were not loaded or lie beyond the context must be finite ----
         if (t == n - 1) {
           const int zero_from = min(nblk_need * kBS, ctx) - kbase;
@@ -260,9 +258,33 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
             fence_proxy_async();
           }
         }
-        tmem_wait_st();
-        tc_fence_before();
-        mbar_arrive(bar(kBarPReady + w));
+        PA_TRACE(5 * w + 2, t);
+        const uint64_t negm2 = pack2(-m_used, -m_used);
+        uint64_t sum2[2] = {pack2(0.f, 0.f), pack2(0.f, 0.f)};
+        // exponentiate in place: v[c] <- bf16x2(p[2c], p[2c + 1]); P = first 64 columns of S.  The two
+        // 64-key halves are published separately so P V starts while the second half is exponentiated.
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+#pragma unroll
+          for (int c = hf * 32; c < hf * 32 + 32; ++c) {
+            float x0, x1;
+            unpack2(ffma2(pack2(__uint_as_float(v[2 * c]), __uint_as_float(v[2 * c + 1])), scale2, negm2), x0, x1);
+            const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+            sum2[c & 1] = fadd2(sum2[c & 1], pack2(p0, p1));
+            v[c] = pack_bf16(p0, p1);
+          }
+          tmem_st32(tS + hf * 32, v + hf * 32);
+          if (hf == 1) {
+            PA_TRACE(5 * w + 3, t);
+            tmem_wait_st();                                  // also covers the O rescale above
+            tc_fence_before();
+            mbar_arrive(bar(kBarPReady + 2 * w + hf));
+            PA_TRACE(5 * w + 4, t);
+          }
+        }
+        float s0, s1;
+        unpack2(fadd2(sum2[0], sum2[1]), s0, s1);
+        l = l * alpha + (s0 + s1);
       }
 
       // ---- epilogue: O / l -> out ----
@@ -316,60 +338,63 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
     }
   } else if (warp == 9) {
     // =============================== MMA issuer ===============================
-    constexpr uint32_t idesc_s = umma_idesc(kTileN, false);
-    constexpr uint32_t idesc_o = umma_idesc(HD, true);
-    auto wait_item = [&](int item) { mbar_wait(bar(kBarKvFull + item % kRing), (item / kRing) & 1); };
-    auto free_item = [&](int item) {
-      if (lane == 0) umma_commit(bar(kBarKvEmpty + item % kRing));
-      __syncwarp();
-    };
-    auto qk = [&](int w, int t) {                            // S_w = Q_w K(t)^T   (both operands in shared memory)
-      if (lane == 0) {
-        const uint32_t a0 = sQ + (uint32_t)w * kItem, b0 = sRing + (uint32_t)((2 * t) % kRing) * kItem;
+    // ONE elected thread runs the whole role (waits included): every tcgen05 operand then lives in
+    // uniform registers and an MMA costs a handful of issue slots instead of an election loop.
+    if (elect_one()) {
+      constexpr uint32_t idesc_s = umma_idesc(kTileN, false);
+      constexpr uint32_t idesc_o = umma_idesc(HD, true);
+      constexpr uint64_t kDescK = ((uint64_t)(16 >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+      constexpr uint64_t kDescV = ((uint64_t)(kSlab >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+      const bool tr = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+      auto wait_item = [&](int item) { mbar_wait(bar(kBarKvFull + item % kRing), (item / kRing) & 1); };
+      auto free_item = [&](int item) { umma_commit(bar(kBarKvEmpty + item % kRing)); };
+      auto qk = [&](int w, int t) {                          // S_w = Q_w K(t)^T   (both operands in shared memory)
+        if (tr && t < kTraceTiles) p.trace[t * kTraceSlots + 11 + 2 * w] = clock64();
+        const uint64_t da = kDescK | (uint64_t)(((sQ + (uint32_t)w * kItem) & 0x3FFFFu) >> 4);
+        const uint64_t db = kDescK | (uint64_t)(((sRing + (uint32_t)((2 * t) % kRing) * kItem) & 0x3FFFFu) >> 4);
+        const uint32_t d = tmem + (uint32_t)w * 128u;
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
-          const uint32_t koff = (uint32_t)(kk >> 2) * kSlab + (uint32_t)(kk & 3) * 32u;
-          umma_bf16(tmem + (uint32_t)w * 128u, umma_desc(a0 + koff, 16, 1024), umma_desc(b0 + koff, 16, 1024), idesc_s, kk > 0);
+          const uint64_t koff = (uint64_t)(((uint32_t)(kk >> 2) * kSlab + (uint32_t)(kk & 3) * 32u) >> 4);
+          umma_bf16(d, da + koff, db + koff, idesc_s, kk > 0);
         }
         umma_commit(bar(kBarSFull + w));
-      }
-      __syncwarp();
-    };
-    auto pv = [&](int w, int t, bool last) {                 // O_w += P_w V(t)      (P in TMEM, V in shared memory)
-      mbar_wait(bar(kBarPReady + w), t & 1);
-      tc_fence_after();
-      if (lane == 0) {
-        const uint32_t b0 = sRing + (uint32_t)((2 * t + 1) % kRing) * kItem;
+      };
+      auto pv = [&](int w, int t, bool last) {               // O_w += P_w V(t)      (P in TMEM, V in shared memory)
+        mbar_wait(bar(kBarPReady + 2 * w + 1), t & 1);
+        if (tr && t < kTraceTiles) p.trace[t * kTraceSlots + 10 + 2 * w] = clock64();
+        tc_fence_after();
+        const uint64_t db = kDescV | (uint64_t)(((sRing + (uint32_t)((2 * t + 1) % kRing) * kItem) & 0x3FFFFu) >> 4);
+        const uint32_t d = tmem + kTmemO + (uint32_t)w * 128u, a = tmem + (uint32_t)w * 128u;
+        umma_bf16_ts(d, a, db, idesc_o, t > 0 ? 1u : 0u);
 #pragma unroll
-        for (int ks = 0; ks < kTileN / 16; ++ks)
-          umma_bf16_ts(tmem + kTmemO + (uint32_t)w * 128u, tmem + (uint32_t)w * 128u + (uint32_t)ks * 8u,
-                       umma_desc(b0 + (uint32_t)ks * (16 * 128), kSlab, 1024), idesc_o, (t > 0 || ks > 0) ? 1u : 0u);
+        for (int ks = 1; ks < kTileN / 16; ++ks) umma_bf16_ts(d, a + (uint32_t)ks * 8u, db + (uint64_t)(ks * (16 * 128 >> 4)), idesc_o, 1u);
         if (last) umma_commit(bar(kBarODone + w));
+      };
+      mbar_wait(bar(kBarQReady), 0);
+      if (ntok_b > 0) mbar_wait(bar(kBarQReady + 1), 0);
+      tc_fence_after();
+      wait_item(0);
+      qk(0, 0);
+      if (n_b > 0) qk(1, 0);
+      free_item(0);
+      for (int t = 0; t < n; ++t) {
+        wait_item(2 * t + 1);                                // V(t)
+        if (t + 1 < n) wait_item(2 * t + 2);                 // K(t + 1)
+        if (t < n_a) {
+          pv(0, t, t == n_a - 1);
+          if (t + 1 < n_a) qk(0, t + 1);
+        }
+        if (t < n_b) {
+          pv(1, t, t == n_b - 1);
+          if (t + 1 < n_b) qk(1, t + 1);
+        }
+        free_item(2 * t + 1);
+        if (t + 1 < n) free_item(2 * t + 2);
       }
-      __syncwarp();
-    };
-    mbar_wait(bar(kBarQReady), 0);
-    if (ntok_b > 0) mbar_wait(bar(kBarQReady + 1), 0);
-    tc_fence_after();
-    wait_item(0);
-    qk(0, 0);
-    if (n_b > 0) qk(1, 0);
-    free_item(0);
-    for (int t = 0; t < n; ++t) {
-      wait_item(2 * t + 1);                                  // V(t)
-      if (t + 1 < n) wait_item(2 * t + 2);                   // K(t + 1)
-      if (t < n_a) {
-        pv(0, t, t == n_a - 1);
-        if (t + 1 < n_a) qk(0, t + 1);
-      }
-      if (t < n_b) {
-        pv(1, t, t == n_b - 1);
-        if (t + 1 < n_b) qk(1, t + 1);
-      }
-      free_item(2 * t + 1);
-      if (t + 1 < n) free_item(2 * t + 2);
+      tc_fence_before();
     }
-    tc_fence_before();
+    __syncwarp();
   }
   }
 
@@ -416,5 +441,29 @@ int pa_launch_prefill_tc2(const PaPrefillParams& p_in, cudaStream_t stream) {
   rc = pa_get_kv_tensor_map(p.v, kv, 1, &mv, &ph);
   if (rc) return rc;
   p.pos_head = ph;
-  return p.head_dim == 128 ? launch<128>(p, mk, mv, stream) : launch<64>(p, mk, mv, stream);
+  p.trace = nullptr;
+  static const bool trace = getenv("PA_PREFILL_TRACE") != nullptr;
+  if (!trace) return p.head_dim == 128 ? launch<128>(p, mk, mv, stream) : launch<64>(p, mk, mv, stream);
+  // bring-up aid: clock64 stamps of the first tiles of CTA (0,0,0), printed as deltas to stderr
+  static long long* dbuf = nullptr;
+  const size_t nbytes = (size_t)kTraceTiles * kTraceSlots * sizeof(long long);
+  if (!dbuf && cudaMalloc(&dbuf, nbytes) != cudaSuccess) return -5;
+  cudaMemsetAsync(dbuf, 0, nbytes, stream);
+  p.trace = dbuf;
+  rc = p.head_dim == 128 ? launch<128>(p, mk, mv, stream) : launch<64>(p, mk, mv, stream);
+  static int printed = 0;
+  if (rc == 0 && printed++ == 3) {
+    static long long h[kTraceTiles * kTraceSlots];
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(h, dbuf, nbytes, cudaMemcpyDeviceToHost);
+    const long long t0 = h[0];
+    fprintf(stderr, "tile | A: sfull ld max exp arrive | B: sfull ld max exp arrive | MMA: pA qkA pB qkB  (cycles since A's first S)\n");
+    for (int t = 0; t < kTraceTiles; ++t) {
+      fprintf(stderr, "%3d |", t);
+      for (int k = 0; k < 14; ++k)
+        fprintf(stderr, " %7lld%s", h[t * kTraceSlots + k] ? h[t * kTraceSlots + k] - t0 : -1, (k == 4 || k == 9) ? " |" : "");
+      fprintf(stderr, "\n");
+    }
+  }
+  return rc;
 }
