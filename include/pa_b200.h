@@ -162,6 +162,21 @@ int pa_swap_blocks(void* dst_base, int64_t dst_plane_stride_bytes, int64_t dst_b
                    const int64_t* pairs_host, int32_t num_pairs, int32_t direction,
                    void* stream);
 
+/* Staged swap for scattered device blocks: a gather kernel packs the device
+ * blocks of the pairs into `staging` (device memory, laid out
+ * [plane][pair][block_bytes], >= num_planes * num_pairs * block_bytes) at HBM
+ * speed, then ONE pinned cudaMemcpyAsync per (plane, run of consecutive HOST
+ * blocks) crosses the link; swap-in is the mirror image (copies, then a scatter
+ * kernel).  Everything is ordered on `stream`; nothing synchronises.  Host
+ * blocks must be dense (host_block_stride_bytes == block_bytes).  `pairs_host`
+ * and `pairs_dev` hold the same int64 [num_pairs, 2] (src_block, dst_block) in
+ * host and device memory.  direction as for pa_swap_blocks.                   */
+int pa_swap_blocks_staged(void* dev_base, int64_t dev_plane_stride_bytes, int64_t dev_block_stride_bytes,
+                          void* host_base, int64_t host_plane_stride_bytes, int64_t host_block_stride_bytes,
+                          int32_t num_planes, int64_t block_bytes,
+                          const int64_t* pairs_host, const int64_t* pairs_dev, int32_t num_pairs,
+                          int32_t direction, void* staging, int64_t staging_bytes, void* stream);
+
 /* ---- prefill attention (replaces the attention half of
  *      paged_attention_prefill, paged_attention.py:125-136, extended with
  *      history: query chunk at positions [start_pos, start_pos + num_tokens)

@@ -54,6 +54,32 @@ class OracleOps:
                                       compute_dtype=torch.float64).to(query.dtype)
 
 
+    # swap space for kv_manager (CPU stand-ins of HostKVPool / swap_out / swap_in)
+    class HostKVPool:
+        def __init__(self, like, num_blocks, block_dim=None):
+            bd = like.dim() - 4 if block_dim is None else block_dim
+            shape = list(like.shape)
+            shape[bd] = num_blocks
+            self.kv_cache = torch.zeros(shape, dtype=like.dtype)
+            self.free_blocks = list(range(num_blocks))
+
+        def allocate(self, n):
+            if len(self.free_blocks) < n:
+                raise RuntimeError(f"OOM: need {n}, have {len(self.free_blocks)}")
+            return [self.free_blocks.pop(0) for _ in range(n)]
+
+        def free(self, ids):
+            self.free_blocks.extend(ids)
+
+    @staticmethod
+    def swap_out(dev_cache, host_cache, pairs, block_dim=None):
+        O.swap_blocks(dev_cache, host_cache, pairs, dev_cache.dim() - 4 if block_dim is None else block_dim)
+
+    @staticmethod
+    def swap_in(host_cache, dev_cache, pairs, block_dim=None):
+        O.swap_blocks(host_cache, dev_cache, pairs, dev_cache.dim() - 4 if block_dim is None else block_dim)
+
+
 # ---------------------------------------------------------------------------------------
 # TinyEngine
 # ---------------------------------------------------------------------------------------
@@ -70,6 +96,13 @@ class Req:
     @property
     def in_prefill(self) -> bool:
         return self.num_computed_tokens < len(self.prompt_token_ids)
+
+    # the reference Request's names for the same things (kv_manager is duck-typed on them)
+    is_prefill = in_prefill
+
+    @property
+    def prompt_len(self) -> int:
+        return len(self.prompt_token_ids)
 
 
 @dataclass
@@ -105,16 +138,73 @@ class Blocks:
             self.free.append(b)
 
 
+class HashedBlocks:
+    """Allocator with the INTERFACE of the reference BlockAllocator (allocate(block_hash) ->
+    id | None, free(id), mark_cached(id, hash), num_free, hash_to_block), written from that
+    interface: free blocks are reused oldest-first and keep their hash until reused."""
+
+    def __init__(self, n: int):
+        self.ref_count = [0] * n
+        self.free_order: List[int] = list(range(n))
+        self.hash_to_block: Dict[int, int] = {}
+        self.block_to_hash: Dict[int, int] = {}
+
+    @property
+    def num_free(self) -> int:
+        return len(self.free_order)
+
+    def allocate(self, block_hash: Optional[int] = None) -> Optional[int]:
+        if block_hash is not None and block_hash in self.hash_to_block:
+            b = self.hash_to_block[block_hash]
+            self.ref_count[b] += 1
+            if b in self.free_order:
+                self.free_order.remove(b)
+            return b
+        if not self.free_order:
+            return None
+        b = self.free_order.pop(0)
+        h = self.block_to_hash.pop(b, None)
+        if h is not None:
+            self.hash_to_block.pop(h, None)
+        self.ref_count[b] = 1
+        return b
+
+    def free(self, b: int) -> None:
+        if self.ref_count[b] <= 0:
+            return
+        self.ref_count[b] -= 1
+        if self.ref_count[b] == 0:
+            self.free_order.append(b)
+
+    release = free                                     # TinyScheduler's name
+
+    def mark_cached(self, b: int, block_hash: int) -> None:
+        if block_hash not in self.hash_to_block:
+            self.hash_to_block[block_hash] = b
+            self.block_to_hash[b] = block_hash
+
+    # TinyScheduler's names
+    def take(self) -> Optional[int]:
+        return self.allocate()
+
+
 class TinyScheduler:
     def __init__(self, blocks: Blocks, block_size: int, max_seqs: int, token_budget: int):
         self.blocks, self.bs, self.max_seqs, self.budget = blocks, block_size, max_seqs, token_budget
+        # the reference Scheduler's attribute names (kv_manager is duck-typed on them)
+        self.allocator, self.block_size = blocks, block_size
+        self.max_num_seqs, self.max_num_batched_tokens = max_seqs, token_budget
         self.waiting: List[Req] = []
         self.running: List[Req] = []
         self.paused: List[Req] = []          # swapped out: not scheduled until resumed
 
-    def _grow(self, r: Req, upto_tokens: int) -> None:
+    def _grow(self, r: Req, upto_tokens: int) -> bool:
         while len(r.block_table) * self.bs < upto_tokens:
-            r.block_table.append(self.blocks.take())
+            b = self.blocks.take()
+            if b is None:                            # reference behaviour: the request sits this step out
+                return False
+            r.block_table.append(b)
+        return True
 
     def _slots(self, r: Req, start: int, n: int) -> List[int]:
         return [r.block_table[p // self.bs] * self.bs + p % self.bs for p in range(start, start + n)]
@@ -136,7 +226,10 @@ class TinyScheduler:
                 toks = r.prompt_token_ids[start:start + n]
             else:
                 n, toks = 1, [r.output_token_ids[-1]]
-            self._grow(r, start + n)
+            if not self._grow(r, start + n):
+                if r in fresh:
+                    fresh.remove(r)
+                continue
             out.append(Sched(r, toks, list(range(start, start + n)), r.in_prefill, self._slots(r, start, n)))
             budget -= n
         for r in fresh:
@@ -223,11 +316,11 @@ class TinyModel(nn.Module):
 
 class TinyEngine:
     def __init__(self, vocab=200, hidden=128, layers=2, heads=4, inter=256, num_blocks=64, block_size=16,
-                 max_seqs=8, token_budget=48, device="cpu", dtype=torch.float32, seed=0):
+                 max_seqs=8, token_budget=48, device="cpu", dtype=torch.float32, seed=0, hashed_blocks=False):
         torch.manual_seed(seed)
         self.device = torch.device(device)
         self.block_size = block_size
-        self.blocks = Blocks(num_blocks)
+        self.blocks = HashedBlocks(num_blocks) if hashed_blocks else Blocks(num_blocks)
         self.scheduler = TinyScheduler(self.blocks, block_size, max_seqs, token_budget)
         self.model = TinyModel(vocab, hidden, layers, heads, inter, num_blocks, block_size).to(self.device).to(dtype)
         self.logits_log: Dict[str, List[torch.Tensor]] = {}

@@ -508,6 +508,41 @@ def test_swap_out_in_round_trip(P):
     assert torch.equal(after[:, :, untouched], before[:, :, untouched])
 
 
+@pytest.mark.parametrize("layout", ["pool", "layer", "engine"])
+@pytest.mark.parametrize("staging_bytes", [None, 96 << 10], ids=["one-chunk", "chunked"])
+def test_swap_scattered_blocks_staged_path(P, layout, staging_bytes, monkeypatch):
+    # many scattered device blocks <-> consecutive host blocks: the staged path (gather kernel ->
+    # dense staging -> one pinned copy per (plane, host run)); a tiny staging cap forces chunking
+    if staging_bytes is not None:
+        monkeypatch.setattr(P, "_SWAP_STAGING_BYTES", staging_bytes)
+    g = torch.Generator().manual_seed(12)
+    nb, nh = 96, 48
+    if layout == "pool":
+        dev = torch.randn(2, 3, nb, 2, 16, 64, generator=g).to(torch.bfloat16).to(DEV)   # [2, L, NB, Hkv, BS, D]
+    elif layout == "layer":
+        dev = torch.randn(2, 3, nb, 2, 16, 64, generator=g).to(torch.bfloat16).to(DEV)[:, 1]
+    else:
+        dev = torch.randn(3, nb, 16, 2, 64, generator=g).to(torch.float32).to(DEV)      # [L, NB, BS, H, D]
+    bd = dev.dim() - 4
+    before = dev.cpu().clone()
+    host = P.HostKVPool(dev, num_blocks=nh)
+    host.kv_cache.zero_()
+    dev_blocks = torch.randperm(nb, generator=g)[:40].tolist()
+    host_blocks = host.allocate(30) + [40, 45, 41, 47, 33, 32, 31, 46, 44, 42]       # a long run + scattered tail
+    P.swap_out(dev, host.kv_cache, list(zip(dev_blocks, host_blocks))).synchronize()
+    ref_host = torch.zeros_like(host.kv_cache)
+    O.swap_blocks(before, ref_host, list(zip(dev_blocks, host_blocks)), block_dim=bd)
+    assert torch.equal(host.kv_cache.view(torch.uint8), ref_host.view(torch.uint8))
+    # back into other scattered blocks
+    dev.index_fill_(bd, torch.tensor(dev_blocks, device=DEV), 0)
+    new_blocks = torch.randperm(nb, generator=g)[:40].tolist()
+    torch.cuda.current_stream().wait_event(P.swap_in(host.kv_cache, dev, list(zip(host_blocks, new_blocks))))
+    expect = before.clone()
+    expect.index_fill_(bd, torch.tensor(dev_blocks), 0)
+    O.swap_blocks(ref_host, expect, list(zip(host_blocks, new_blocks)), block_dim=bd)
+    assert torch.equal(dev.cpu().view(torch.uint8), expect.view(torch.uint8))
+
+
 def test_swap_then_decode_matches(P):
     # decode -> swap the sequence out -> swap it into other blocks -> decode: identical bits
     q, kv, bts, lens = _full_case(2, 500, 900, seed=8, nb_spare=80)

@@ -50,6 +50,8 @@ SIGNATURES = {
     "pa_copy_blocks": (c_int, [c_void_p, c_int64, c_int32, c_int64, c_int64, c_void_p, c_int32, c_void_p]),
     "pa_swap_blocks": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int32, c_int64,
                                c_void_p, c_int32, c_int32, c_void_p]),
+    "pa_swap_blocks_staged": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int32, c_int64,
+                                      c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_int64, c_void_p]),
     "pa_prefill_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
     "pa_prefill": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
                            c_void_p, c_int32, c_int32, c_int32, c_void_p, c_size_t, c_void_p]),

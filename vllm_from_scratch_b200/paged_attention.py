@@ -597,6 +597,20 @@ def _side_stream(device: torch.device) -> torch.cuda.Stream:
     return s
 
 
+_SWAP_STAGING_BYTES = 256 << 20      # upper bound of the device staging area of a staged swap
+_swap_stages = {}
+
+
+def _swap_staging(device: torch.device, nbytes: int) -> torch.Tensor:
+    """Per-device staging area of the staged swap (grown on demand, reused across calls; every
+    use is ordered on the swap stream, so reuse needs no extra synchronisation)."""
+    t = _swap_stages.get(device.index)
+    if t is None or t.numel() < nbytes:
+        t = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        _swap_stages[device.index] = t
+    return t
+
+
 def _swap(dst: torch.Tensor, src: torch.Tensor, pairs, block_dim: Optional[int], direction: int,
           stream: Optional[torch.cuda.Stream]) -> torch.cuda.Event:
     dev_t = src if direction == 0 else dst
@@ -623,12 +637,41 @@ def _swap(dst: torch.Tensor, src: torch.Tensor, pairs, block_dim: Optional[int],
             db, dbs, dg = _plane_groups(dst, bd)
             if sb != db or len(sg) != len(dg) or any(a[1] != b[1] for a, b in zip(sg, dg)):
                 raise ValueError("swap: source and destination plane structures differ")
-            arr = (ctypes.c_int64 * (2 * len(pl)))(*[x for p in pl for x in p])
             lib = _lib.load()
-            for (soff, planes, sps), (doff, _, dps) in zip(sg, dg):
-                rc = lib.pa_swap_blocks(dst.data_ptr() + doff, dps, dbs, src.data_ptr() + soff, sps, sbs,
-                                        planes, sb, ctypes.addressof(arr), len(pl), direction, side.cuda_stream)
-                _lib.check(rc, "pa_swap_blocks")
+            hcol = 1 if direction == 0 else 0
+            both_runs = 1 + sum(1 for a, b in zip(pl, pl[1:]) if b[0] != a[0] + 1 or b[1] != a[1] + 1)
+            host_runs = 1 + sum(1 for a, b in zip(pl, pl[1:]) if b[hcol] != a[hcol] + 1)
+            (h_bs, d_bs) = (dbs, sbs) if direction == 0 else (sbs, dbs)
+            planes_total = sum(g[1] for g in sg)
+            staged = (both_runs >= 8 and host_runs * planes_total < both_runs * len(sg) and h_bs == sb
+                      and sb % 16 == 0 and d_bs % 16 == 0)
+            if staged:
+                # scattered device blocks: gather kernel -> dense staging -> one pinned copy per
+                # (plane, run of host blocks); mirror image for swap-in.  Chunked by staging size.
+                per_pair = sb * max(g[1] for g in sg)
+                chunk = max(1, min(len(pl), _SWAP_STAGING_BYTES // per_pair, 65535))
+                stage = _swap_staging(dev_t.device, min(len(pl), chunk) * per_pair)
+                for at in range(0, len(pl), chunk):
+                    part = pl[at:at + chunk]
+                    flat = [x for p in part for x in p]
+                    arr = (ctypes.c_int64 * len(flat))(*flat)
+                    with torch.cuda.stream(side):
+                        # pageable -> device: staged by the driver before the call returns and
+                        # ordered on the swap stream, so neither buffer outlives its use
+                        pairs_dev = torch.tensor(flat, dtype=torch.int64).to(dev_t.device)
+                    for (soff, planes, sps), (doff, _, dps) in zip(sg, dg):
+                        (d_ptr, d_ps, h_ptr, h_ps) = (src.data_ptr() + soff, sps, dst.data_ptr() + doff, dps) \
+                            if direction == 0 else (dst.data_ptr() + doff, dps, src.data_ptr() + soff, sps)
+                        rc = lib.pa_swap_blocks_staged(d_ptr, d_ps, d_bs, h_ptr, h_ps, h_bs, planes, sb,
+                                                       ctypes.addressof(arr), pairs_dev.data_ptr(), len(part), direction,
+                                                       stage.data_ptr(), stage.numel(), side.cuda_stream)
+                        _lib.check(rc, "pa_swap_blocks_staged")
+            else:
+                arr = (ctypes.c_int64 * (2 * len(pl)))(*[x for p in pl for x in p])
+                for (soff, planes, sps), (doff, _, dps) in zip(sg, dg):
+                    rc = lib.pa_swap_blocks(dst.data_ptr() + doff, dps, dbs, src.data_ptr() + soff, sps, sbs,
+                                            planes, sb, ctypes.addressof(arr), len(pl), direction, side.cuda_stream)
+                    _lib.check(rc, "pa_swap_blocks")
         ev.record(side)
     return ev
 
