@@ -385,7 +385,7 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(torch, pool.kv_cache[:, 0].cpu(), bts_h, lens_h, q_h, wl, args.cpu_seconds)
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -491,11 +491,31 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_JSON_FD = None
+
+
+def emit(line) -> None:
+    """The ONE JSON line goes to the process's original stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
 
 
 def main():
+    global _JSON_FD
     args = parse_args()
+    # Libraries write to fd 1 behind Python's back (NCCL prints its version banner there on
+    # communicator creation): point fd 1 at stderr for the whole run and keep the real stdout
+    # for the one JSON line.
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if os.environ.get("BENCH_DEBUG"):
         import faulthandler
         faulthandler.dump_traceback_later(int(os.environ.get("BENCH_DEBUG_AFTER", "60")), exit=True)
