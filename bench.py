@@ -57,6 +57,9 @@ def parse_args():
                     help="N > 1: 'seq' = every rank its own sequences (weak scaling, no collective); 'head' = "
                          "every rank Hkv / N KV heads of the SAME batch + one NCCL all-gather of the outputs "
                          "(strong scaling; default workload c3)")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="--shard head: 'peer' = output gather fused into the decode kernel over NVLink peer memory "
+                         "(default); 'nccl' = decode kernel + one NCCL all-gather")
     ap.add_argument("--layers", type=int, default=0, help="per-layer caches the loop rotates over")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (default min(steps, 300))")
     ap.add_argument("--ramp-ms", type=float, default=300.0, help="untimed clock ramp before the warm-up steps")
@@ -233,20 +236,49 @@ def run_ours(args):
         from vllm_from_scratch_b200 import sharding as S
         hq_full = hq
         hkv, hq = len(S.shard_kv_heads(hkv, world, rank)), len(S.shard_q_heads(hq, hkv, world, rank))
+        hkv_full = wl[3]
         wl = (b, ctx, hq, hkv, d, bs, def_layers, desc)
-        gather = S.HeadGather(b, hq_full, d, torch.bfloat16, dev, world=world, rank=rank)
+        if args.gather == "peer":
+            # output gather fused into the decode kernel: rows go to every rank's buffer over NVLink
+            # peer memory, arrival counters instead of a collective (sharding.PeerGather)
+            gather = S.PeerGather(b, hq_full, hkv_full, d, dev, world=world, rank=rank)
+        else:
+            gather = S.HeadGather(b, hq_full, d, torch.bfloat16, dev, world=world, rank=rank)
     pool, bts_h, lens_h, q_h, k_h, v_h, slots_h = make_workload(torch, dev, wl, layers,
                                                                 seed=1234 + (0 if head_mode else rank))
     bts, lens, q = bts_h.to(dev), lens_h.to(dev), q_h.to(dev)
+    peer_mode = head_mode and args.gather == "peer"
     out = gather.local_out() if head_mode else torch.empty_like(q)
     ws = P.new_decode_workspace(b, hq, hkv, d, dev)
     caches = [pool.layer(i) for i in range(layers)]
     kv_bytes, io_bytes = algorithmic_bytes(b, ctx, hq, hkv, d, bs)
 
     def step(i):
+        if peer_mode:
+            gather.decode(q, caches[i % layers], bts, lens, workspace=ws, parity=i % 2)   # decode + fused gather + wait
+            return
         P.paged_attention_decode_batched(q, caches[i % layers], bts, lens, out=out, workspace=ws)
         if head_mode:
             gather.all_gather()             # the kernel wrote its slice of the gather buffer in place
+
+    step_eager = step
+    if peer_mode:
+        # decode + fused gather + arrival wait per layer cache as CUDA graphs (the wait's step number
+        # lives on the device): at 8 GPUs the kernel is shorter than the host launch path
+        if layers % 2:
+            raise SystemExit("--gather peer needs an even --layers (the two gather buffer sets alternate)")
+        for i in range(2 * layers):                        # eager first: tensor maps, workspaces; even count
+            step_eager(i)
+        torch.cuda.synchronize()
+        graphs = []
+        for i in range(layers):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                gather.decode(q, caches[i], bts, lens, workspace=ws, parity=i % 2)
+            graphs.append(gr)
+
+        def step(i):                                       # noqa: F811
+            graphs[i % layers].replay()
 
     def barrier():
         if world > 1:
@@ -257,7 +289,8 @@ def run_ours(args):
     # untimed: ramp clocks, fault in the tensor maps, then the W warm-up steps
     t_end = time.perf_counter() + args.ramp_ms * 1e-3
     i = 0
-    while time.perf_counter() < t_end:
+    # head mode: every rank must run the SAME number of steps (collective / arrival counts)
+    while (i < int(args.ramp_ms * 4)) if head_mode else (time.perf_counter() < t_end):
         step(i)
         i += 1
         if i % 64 == 0:
@@ -285,7 +318,7 @@ def run_ours(args):
     nprof = min(args.steps, 512)
     lib.pa_profile_begin(nprof)
     for i in range(nprof):
-        step(i)
+        step_eager(i)
     import ctypes
     dec_ms = (ctypes.c_float * nprof)()
     red_ms = (ctypes.c_float * nprof)()
@@ -316,7 +349,28 @@ def run_ours(args):
         steps_e2e.append(st)
     h2d, d2h = steps_e2e[0].h2d_bytes, steps_e2e[0].d2h_bytes
 
+    if peer_mode:
+        # host buffers in, gathered host buffer out, through sharding.PeerGather: one staged H2D copy of
+        # q + new K / V rows (+ slots), slot write, decode with the fused gather, D2H of ALL ranks' rows
+        pin = lambda t: t.contiguous().pin_memory()                                     # noqa: E731
+        hq_p, hk_p, hv_p, hs_p = pin(q_h), pin(k_h), pin(v_h), pin(slots_h)
+        k_d, v_d, s_d = k_h.to(dev), v_h.to(dev), slots_h.to(dev)
+        full_h = torch.empty((world, b, hq, d), dtype=torch.bfloat16).pin_memory()
+        h2d = sum(t.numel() * t.element_size() for t in (hq_p, hk_p, hv_p, hs_p))
+        d2h = full_h.numel() * full_h.element_size()
+
+    def e2e_step_peer(i):
+        q.copy_(hq_p, non_blocking=True)
+        k_d.copy_(hk_p, non_blocking=True)
+        v_d.copy_(hv_p, non_blocking=True)
+        s_d.copy_(hs_p, non_blocking=True)
+        P.reshape_and_cache(k_d, v_d, caches[i % layers], s_d)
+        full_h.copy_(gather.decode(q, caches[i % layers], bts, lens, workspace=ws, parity=i % 2), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
     def e2e_step(i):
+        if peer_mode:
+            return e2e_step_peer(i)
         st = steps_e2e[i % layers]
         st.replay()
         if head_mode:
@@ -358,8 +412,10 @@ def run_ours(args):
         "config": {"workload": desc, "seqs_per_gpu": b, "context": ctx, "num_q_heads": hq, "num_kv_heads": hkv,
                    "head_dim": d, "block_size": bs, "kv_layout": "[2, L, NB, Hkv, BS, D] (reference pool)",
                    "block_tables": "seeded randperm, fully scattered",
-                   "parallelism": (f"KV-head-sharded x{world}: {hkv} KV / {hq} Q heads per GPU, one NCCL "
-                                   f"all-gather of [B, Hq/{world}, D] per step" if head_mode else
+                   "parallelism": (f"KV-head-sharded x{world}: {hkv} KV / {hq} Q heads per GPU, " +
+                                   ("output gather fused into the decode kernel (NVLink peer stores + arrival "
+                                    "counters, no collective call)" if peer_mode else
+                                    f"one NCCL all-gather of [B, Hq/{world}, D] per step") if head_mode else
                                    f"sequence-sharded x{world}, one pool per GPU, no collective"),
                    "l2": f"inputs larger than L2: loop rotates over {layers} per-layer caches of "
                          f"{kv_bytes / 2**20:.0f} MiB each",

@@ -102,6 +102,60 @@ int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h,
               void* workspace, size_t workspace_bytes,
               void* stream /* cudaStream_t */);
 
+/* ---- decode fused with the output gather of KV-head-sharded decode ---------
+ * (rank r owns KV heads [r Hkv/P, (r+1) Hkv/P) of every
+ * block; the only exchange on the path is the gather of the [B, Hq/P, D]
+ * outputs.)  Same as pa_decode, and in the SAME kernel every final output row
+ * is also stored - plain stores over NVLink peer memory - into this rank's slot
+ * of each remote rank's gather buffer (remote_out[r]: same strides as `out`),
+ * and every completed (sequence, KV head) segment is counted, release at system
+ * scope, into this rank's arrival counter on every rank (remote_sig[r], and
+ * local_sig on this rank).  No collective call, no second kernel on the sender.
+ * The consumer orders itself with pa_peer_wait: counters are monotonic, after
+ * step n (1-based) each holds n * batch * num_kv_heads.  Buffers must alternate
+ * between two sets from step to step (a fast rank may run one step ahead).
+ * Fast path only (bf16, block_size 16, head_dim 64 / 128): PA_ERR_UNSUPPORTED
+ * otherwise.                                                                  */
+#define PA_MAX_REMOTE_PEERS 7
+typedef struct {
+  int32_t num_remote;                          /* ranks other than this one, <= 7 */
+  void* remote_out[PA_MAX_REMOTE_PEERS];
+  uint32_t* remote_sig[PA_MAX_REMOTE_PEERS];
+  uint32_t* local_sig;
+} PaPeerGather;
+
+int pa_decode_gather(const void* q, int64_t q_stride_b, int64_t q_stride_h,
+                     void* out, int64_t o_stride_b, int64_t o_stride_h,
+                     const PaKvCache* cache,
+                     const int32_t* block_tables, int32_t bt_stride,
+                     const int32_t* seq_lens,
+                     int32_t batch, int32_t num_q_heads,
+                     void* workspace, size_t workspace_bytes,
+                     const PaPeerGather* peers, void* stream);
+
+/* One small kernel on `stream`: returns once local_sig[r] >= expected for every
+ * r < world (ld.acquire.sys), so later work on the stream sees all ranks' rows.
+ * Bounded: after timeout_us it writes 1 + r (the late rank) to *status (device
+ * int32, may be null) and returns instead of hanging the GPU.                 */
+int pa_peer_wait(const uint32_t* local_sig, int32_t world, uint32_t expected,
+                 int64_t timeout_us, int32_t* status, void* stream);
+
+/* Same, with the step number kept on the device: waits for (*epoch + 1) *
+ * segments, then advances *epoch (uint32 in device memory, zero at the start).
+ * No per-step host argument, so decode + wait can be captured in a CUDA graph. */
+int pa_peer_wait_next(const uint32_t* local_sig, int32_t world, uint32_t* epoch,
+                      uint32_t segments, int64_t timeout_us, int32_t* status,
+                      void* stream);
+
+/* Peer-visible device memory for the gather buffers and counters (the one place
+ * the library allocates: cudaMalloc, zero-filled, plus its 64-byte CUDA IPC
+ * handle).  Another process of the same node maps it with pa_peer_open (peer
+ * access is enabled on first use) and unmaps it with pa_peer_close.           */
+int pa_peer_alloc(size_t bytes, void** ptr, void* ipc_handle_64);
+int pa_peer_open(const void* ipc_handle_64, void** ptr);
+int pa_peer_close(void* ptr);
+int pa_peer_free(void* ptr);
+
 /* ---- slot mapping on the device (replaces compute_slot_mapping,
  *      paged_attention.py:54-64, and Scheduler._compute_slot_mapping,
  *      mini_vllm.py:209-219): for i in [0, num_tokens)

@@ -32,6 +32,16 @@ class PaKvCache(Structure):
     ]
 
 
+class PaPeerGather(Structure):
+    """Mirror of `struct PaPeerGather` (include/pa_b200.h)."""
+    _fields_ = [
+        ("num_remote", c_int32),
+        ("remote_out", c_void_p * 7),
+        ("remote_sig", c_void_p * 7),
+        ("local_sig", c_void_p),
+    ]
+
+
 # name -> (restype, argtypes); one entry per symbol declared in include/pa_b200.h
 SIGNATURES = {
     "pa_abi_version": (c_int, []),
@@ -42,6 +52,15 @@ SIGNATURES = {
     "pa_decode_workspace_init": (c_int, [c_void_p, c_size_t, c_void_p]),
     "pa_decode": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
                           c_void_p, c_int32, c_void_p, c_int32, c_int32, c_void_p, c_size_t, c_void_p]),
+    "pa_decode_gather": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
+                                 c_void_p, c_int32, c_void_p, c_int32, c_int32, c_void_p, c_size_t,
+                                 POINTER(PaPeerGather), c_void_p]),
+    "pa_peer_wait": (c_int, [c_void_p, c_int32, ctypes.c_uint32, c_int64, c_void_p, c_void_p]),
+    "pa_peer_wait_next": (c_int, [c_void_p, c_int32, c_void_p, ctypes.c_uint32, c_int64, c_void_p, c_void_p]),
+    "pa_peer_alloc": (c_int, [c_size_t, POINTER(c_void_p), c_void_p]),
+    "pa_peer_open": (c_int, [c_void_p, POINTER(c_void_p)]),
+    "pa_peer_close": (c_int, [c_void_p]),
+    "pa_peer_free": (c_int, [c_void_p]),
     "pa_slot_mapping": (c_int, [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
     "pa_reshape_and_cache": (c_int, [c_void_p, c_void_p, c_int64, c_int64, POINTER(PaKvCache), c_void_p,
                                      c_int32, c_void_p]),

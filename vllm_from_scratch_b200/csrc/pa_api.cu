@@ -140,10 +140,10 @@ extern "C" int pa_decode_workspace_init(void* workspace, size_t workspace_bytes,
                                                                                                         : PA_ERR_CUDA;
 }
 
-extern "C" int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h, void* out, int64_t o_stride_b,
-                         int64_t o_stride_h, const PaKvCache* cache, const int32_t* block_tables,
-                         int32_t bt_stride, const int32_t* seq_lens, int32_t batch, int32_t num_q_heads,
-                         void* workspace, size_t workspace_bytes, void* stream) {
+static int decode_impl(const void* q, int64_t q_stride_b, int64_t q_stride_h, void* out, int64_t o_stride_b,
+                       int64_t o_stride_h, const PaKvCache* cache, const int32_t* block_tables,
+                       int32_t bt_stride, const int32_t* seq_lens, int32_t batch, int32_t num_q_heads,
+                       void* workspace, size_t workspace_bytes, const PaPeerGather* peers, void* stream) {
   if (batch < 0 || !cache) return PA_ERR_BAD_ARG;
   if (batch == 0) return PA_OK;
   if (!q || !out || !cache->k || !cache->v || !block_tables || !seq_lens || !workspace) return PA_ERR_BAD_ARG;
@@ -158,6 +158,20 @@ extern "C" int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h, 
   if (sms <= 0) return PA_ERR_NO_DEVICE;
 
   PaDecodeParams p;
+  p.num_remote = 0;
+  p.local_sig = nullptr;
+  for (int r = 0; r < 7; ++r) { p.remote_out[r] = nullptr; p.remote_sig[r] = nullptr; }
+  if (peers) {
+    if (peers->num_remote < 0 || peers->num_remote > 7 || !peers->local_sig) return PA_ERR_BAD_ARG;
+    for (int r = 0; r < peers->num_remote; ++r) {
+      if (!peers->remote_out[r] || !peers->remote_sig[r]) return PA_ERR_BAD_ARG;
+      if (reinterpret_cast<uintptr_t>(peers->remote_out[r]) & 3) return PA_ERR_MISALIGNED;
+      p.remote_out[r] = peers->remote_out[r];
+      p.remote_sig[r] = peers->remote_sig[r];
+    }
+    p.num_remote = peers->num_remote;
+    p.local_sig = peers->local_sig;
+  }
   p.q = q; p.out = out; p.k = cache->k; p.v = cache->v;
   p.block_tables = block_tables; p.seq_lens = seq_lens;
   p.q_stride_b = q_stride_b; p.q_stride_h = q_stride_h;
@@ -171,6 +185,7 @@ extern "C" int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h, 
 
   const bool tma = g_force_path.load() != 1 && pa_decode_tma_supported(p, cache->dtype) &&
                    tma_header_fits(batch, Hkv);
+  if (peers && !tma) return PA_ERR_UNSUPPORTED;          // the fused gather lives in the fast-path kernel only
   int ctas = 0;
   int64_t slots;
   int rows;
@@ -213,6 +228,105 @@ extern "C" int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h, 
   if (!tma) rc = pa_launch_reduce(p, cache->dtype, st);      // the TMA kernel merges its own partials
   if (pe) cudaEventRecord(pe[2], st);
   return rc;
+}
+
+extern "C" int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h, void* out, int64_t o_stride_b,
+                         int64_t o_stride_h, const PaKvCache* cache, const int32_t* block_tables,
+                         int32_t bt_stride, const int32_t* seq_lens, int32_t batch, int32_t num_q_heads,
+                         void* workspace, size_t workspace_bytes, void* stream) {
+  return decode_impl(q, q_stride_b, q_stride_h, out, o_stride_b, o_stride_h, cache, block_tables, bt_stride, seq_lens,
+                     batch, num_q_heads, workspace, workspace_bytes, nullptr, stream);
+}
+
+extern "C" int pa_decode_gather(const void* q, int64_t q_stride_b, int64_t q_stride_h, void* out, int64_t o_stride_b,
+                                int64_t o_stride_h, const PaKvCache* cache, const int32_t* block_tables,
+                                int32_t bt_stride, const int32_t* seq_lens, int32_t batch, int32_t num_q_heads,
+                                void* workspace, size_t workspace_bytes, const PaPeerGather* peers, void* stream) {
+  if (!peers) return PA_ERR_BAD_ARG;
+  return decode_impl(q, q_stride_b, q_stride_h, out, o_stride_b, o_stride_h, cache, block_tables, bt_stride, seq_lens,
+                     batch, num_q_heads, workspace, workspace_bytes, peers, stream);
+}
+
+// ---- peer memory plumbing for the fused gather ------------------------------------------
+namespace {
+// Spins until every rank's arrival counter has reached `expected` (counters are monotonic: the
+// caller passes step * segments_per_rank).  Bounded: after `timeout_ns` it records the failure in
+// status[0] and returns instead of hanging the GPU.
+// `epoch` (device counter, may be null): when given, the step number lives on the device - the
+// kernel waits for (epoch + 1) * segments and then advances epoch - so the launch has no
+// per-step host argument and can sit in a CUDA graph.
+__global__ void pa_peer_wait_kernel(const uint32_t* sig, int world, uint32_t expected, unsigned long long timeout_ns,
+                                    int32_t* status, uint32_t* epoch, uint32_t segments) {
+  const int r = threadIdx.x;
+  if (epoch) {
+    const uint32_t e = *reinterpret_cast<volatile uint32_t*>(epoch);
+    expected = (e + 1u) * segments;
+    __syncwarp();
+    if (r == 0) *epoch = e + 1u;
+  }
+  if (r >= world) return;
+  if (status && *reinterpret_cast<volatile int32_t*>(status) != 0) return;   // a peer already failed: do not wait again
+  unsigned long long t0, t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+  for (;;) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(sig + r) : "memory");
+    if ((int32_t)(v - expected) >= 0) break;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    if (t - t0 > timeout_ns) {
+      if (status) atomicExch(status, 1 + r);
+      break;
+    }
+    __nanosleep(64);
+  }
+}
+}  // namespace
+
+extern "C" int pa_peer_wait(const uint32_t* local_sig, int32_t world, uint32_t expected, int64_t timeout_us,
+                            int32_t* status, void* stream) {
+  if (!local_sig || world < 1 || world > 8 || timeout_us <= 0) return PA_ERR_BAD_ARG;
+  pa_peer_wait_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(
+      local_sig, world, expected, (unsigned long long)timeout_us * 1000ull, status, nullptr, 0u);
+  return cudaGetLastError() == cudaSuccess ? PA_OK : PA_ERR_CUDA;
+}
+
+extern "C" int pa_peer_wait_next(const uint32_t* local_sig, int32_t world, uint32_t* epoch, uint32_t segments,
+                                 int64_t timeout_us, int32_t* status, void* stream) {
+  if (!local_sig || !epoch || world < 1 || world > 8 || timeout_us <= 0) return PA_ERR_BAD_ARG;
+  pa_peer_wait_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(
+      local_sig, world, 0u, (unsigned long long)timeout_us * 1000ull, status, epoch, segments);
+  return cudaGetLastError() == cudaSuccess ? PA_OK : PA_ERR_CUDA;
+}
+
+extern "C" int pa_peer_alloc(size_t bytes, void** ptr, void* ipc_handle_64) {
+  if (!ptr || !ipc_handle_64 || bytes == 0) return PA_ERR_BAD_ARG;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* d = nullptr;
+  if (cudaMalloc(&d, bytes) != cudaSuccess) return PA_ERR_CUDA;
+  cudaIpcMemHandle_t h;
+  if (cudaMemset(d, 0, bytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess ||
+      cudaIpcGetMemHandle(&h, d) != cudaSuccess) {
+    cudaFree(d);
+    return PA_ERR_CUDA;
+  }
+  memcpy(ipc_handle_64, &h, 64);
+  *ptr = d;
+  return PA_OK;
+}
+
+extern "C" int pa_peer_open(const void* ipc_handle_64, void** ptr) {
+  if (!ipc_handle_64 || !ptr) return PA_ERR_BAD_ARG;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, ipc_handle_64, 64);
+  return cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess ? PA_OK : PA_ERR_CUDA;
+}
+
+extern "C" int pa_peer_close(void* ptr) {
+  return ptr && cudaIpcCloseMemHandle(ptr) == cudaSuccess ? PA_OK : PA_ERR_CUDA;
+}
+
+extern "C" int pa_peer_free(void* ptr) {
+  return ptr && cudaFree(ptr) == cudaSuccess ? PA_OK : PA_ERR_CUDA;
 }
 
 extern "C" int pa_profile_begin(int32_t max_calls) {

@@ -52,6 +52,13 @@ struct PaDecodeParams {
   int32_t* plan;          // [0] = Q, [1] = total linear blocks, [2 .. 2 + B] = cum[0..B]  (generic path)
   int32_t* counters;      // zero-initialised counter header, left zero by every launch (TMA path)
   long long* dbg;         // optional per-CTA timestamps (pa_decode_debug_times), else null
+  // fused output gather over NVLink peer memory (pa_decode_gather; TMA path only): every final
+  // output row is also stored into this rank's slot of each remote rank's gather buffer, and each
+  // completed (sequence, KV head) segment is counted into this rank's arrival counter on every rank
+  int32_t num_remote;     // 0 = plain pa_decode
+  void* remote_out[7];
+  uint32_t* remote_sig[7];
+  uint32_t* local_sig;    // null = no signalling
 };
 
 struct PaCursor {

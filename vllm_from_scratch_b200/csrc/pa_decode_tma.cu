@@ -57,6 +57,7 @@ constexpr int kDescRing = 8;        // unit descriptors in flight scheduler -> c
 constexpr int kFinRing = 8;         // finished-unit notices in flight consumers -> finisher
 constexpr int kDescBlocks = 64;     // block-table entries per descriptor (longer units span several)
 constexpr int kMaxStages = 8;       // per-warp ring depth cap
+constexpr int kMaxPartials = 32;    // split-K partials per (sequence, KV head) segment, at most
 constexpr int kHeaderInts = 16;     // counter header: [0] unit ticket, [1] exited CTAs, then one int per segment
 constexpr int kMaxBatch = 4096;     // seq_lens + unit prefix sums live in shared memory
 constexpr int kSmemBudget = 227 * 1024;
@@ -223,12 +224,33 @@ __device__ __forceinline__ void build_plan(const int32_t* __restrict__ seq_lens,
     const int nblk = pa_ceil_div(s_len[i], kBS);
     const int remaining = total - s_c[i] * hs;
     int c = max(c_min, 8 * (remaining / (8 * guided_div)));
+    // at most kMaxPartials partials per segment: the merge of a segment is ONE CTA's job at the tail
+    // of the kernel (256 partials of a 32k-token segment cost ~80 us of merging after 35 us of streaming)
+    c = max(c, 8 * pa_ceil_div(nblk, 8 * kMaxPartials));
     c = min(c, 8 * pa_ceil_div(max(nblk, 1), 8));
     s_ucum[i] = pa_ceil_div(nblk, c);
     s_c[i] = c;                     // only this lane touches s_c[i] in this loop
   }
   __syncwarp();
   warp_scan_inplace(s_ucum, batch, lane);
+}
+
+// ---- fused output gather (pa_decode_gather) -------------------------------------------
+// Replicate a final 4-byte output store into this rank's slot of every remote gather buffer
+// (plain stores over NVLink: fire and forget).
+__device__ __forceinline__ void peer_store32(const PaDecodeParams& p, int64_t off_elems, uint32_t v) {
+  for (int r = 0; r < p.num_remote; ++r)
+    *reinterpret_cast<uint32_t*>(static_cast<__nv_bfloat16*>(p.remote_out[r]) + off_elems) = v;
+}
+// Count `n` completed segments into this rank's arrival counter on every rank.  Called by ONE
+// thread after a CTA-scope barrier that follows the segment's stores: the system-scope fence is
+// cumulative, so every store ordered before the barrier is visible to a peer that observes the count.
+__device__ __forceinline__ void peer_signal(const PaDecodeParams& p, uint32_t n) {
+  if (p.local_sig == nullptr) return;
+  __threadfence_system();                 // ONE fence; the counts themselves are relaxed
+  for (int r = 0; r < p.num_remote; ++r)
+    asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(p.remote_sig[r]), "r"(n) : "memory");
+  asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(p.local_sig), "r"(n) : "memory");
 }
 
 template <int HD>
@@ -301,9 +323,15 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     const int NU = s_ucum[p.batch] * hs;
     // sequences with no tokens: defined result is zeros (the reference raises, paged_attention.py:93)
     for (int s = blockIdx.x; s < p.batch; s += gridDim.x)
-      if (s_len[s] == 0)
-        for (int e = lane; e < p.num_q_heads * HD; e += 32)
-          obase[(int64_t)s * p.o_stride_b + (int64_t)(e / HD) * p.o_stride_h + e % HD] = __float2bfloat16_rn(0.f);
+      if (s_len[s] == 0) {
+        for (int e = lane * 2; e < p.num_q_heads * HD; e += 64) {
+          const int64_t off = (int64_t)s * p.o_stride_b + (int64_t)(e / HD) * p.o_stride_h + e % HD;
+          *reinterpret_cast<uint32_t*>(obase + off) = 0u;
+          peer_store32(p, off, 0u);
+        }
+        __syncwarp();
+        if (lane == 0) peer_signal(p, (uint32_t)hs);
+      }
     const __nv_bfloat16* qbase = static_cast<const __nv_bfloat16*>(p.q);
     // One unit of look-ahead: `nx_*` is claimed, located and has its first 64 block-table entries
     // in flight while the current unit is being published.
@@ -459,13 +487,17 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
               }
             }
             const float inv = 1.f / Ls;
-            __nv_bfloat16* op = obase + (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + row) * p.o_stride_h + dq;
-            reinterpret_cast<uint32_t*>(op)[0] = pack_bf16(o.x * inv, o.y * inv);
-            reinterpret_cast<uint32_t*>(op)[1] = pack_bf16(o.z * inv, o.w * inv);
+            const int64_t off = (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + row) * p.o_stride_h + dq;
+            const uint32_t w0 = pack_bf16(o.x * inv, o.y * inv), w1 = pack_bf16(o.z * inv, o.w * inv);
+            reinterpret_cast<uint32_t*>(obase + off)[0] = w0;
+            reinterpret_cast<uint32_t*>(obase + off)[1] = w1;
+            peer_store32(p, off, w0);
+            peer_store32(p, off + 2, w1);
           }
         }
       }
       asm volatile("bar.sync 2, %0;" ::"n"(kFinWarps * 32) : "memory");     // jobs consumed: the leader may refill
+      if (fw == 0 && lane == 0 && njobs > 0) peer_signal(p, (uint32_t)njobs);   // after the barrier: all rows are stored
       if (end) break;
     }
     if (p.dbg && fw == 0 && lane == 0) {
@@ -711,14 +743,17 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       }
       if (nch == 1) {
         const float inv = 1.f / Lsum;
-        *reinterpret_cast<uint32_t*>(obase + (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + head) * p.o_stride_h + dp) =
-            pack_bf16(o0 * inv, o1 * inv);
+        const int64_t off = (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + head) * p.o_stride_h + dp;
+        const uint32_t w0 = pack_bf16(o0 * inv, o1 * inv);
+        *reinterpret_cast<uint32_t*>(obase + off) = w0;
+        peer_store32(p, off, w0);
       } else {
         *reinterpret_cast<float2*>(p.part_o + ((int64_t)slot * g + head) * HD + dp) = make_float2(o0, o1);
         if (dp == 0) p.part_ml[(int64_t)slot * g + head] = make_float2(M, Lsum);
       }
     }
     consumer_bar();                       // B: merge_* are free again; the partial is complete CTA-wide
+    if (nch == 1 && ctid == 0) peer_signal(p, 1u);     // whole segment in one unit: its rows are stored
     ++units_done;
 
     if (nch > 1 && ctid == 0) {

@@ -301,7 +301,7 @@ def decode_workspace_bytes(batch: int, num_q_heads: int, num_kv_heads: int, head
 
 def paged_attention_decode_batched(query: torch.Tensor, kv_cache: KvCacheArg, block_tables: torch.Tensor,
                                    seq_lens: torch.Tensor, out: Optional[torch.Tensor] = None,
-                                   workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
+                                   workspace: Optional[torch.Tensor] = None, peers=None) -> torch.Tensor:
     """Batched decode: for every sequence b, ``softmax(q_b K_b^T / sqrt(D)) V_b`` over the
     ``seq_lens[b]`` tokens reached through ``block_tables[b]`` - i.e. the reference function
     (paged_attention.py:67-101) looped over the batch, in two launches (split-K + reduce).
@@ -311,7 +311,9 @@ def paged_attention_decode_batched(query: torch.Tensor, kv_cache: KvCacheArg, bl
     ``seq_len == 0`` gives zeros.  Output dtype = query's, on the cache's device unless ``out`` is
     given.  ``query`` / ``out`` may also be PINNED host tensors (read / written in place over PCIe).
     A caller-provided ``workspace`` must come from ``new_decode_workspace`` (zero-initialised
-    counter header)."""
+    counter header).  ``peers`` (a ``_lib.PaPeerGather``, built by ``sharding.PeerGather``) fuses the
+    KV-head-sharded output gather into the kernel: rows are also stored into the remote ranks'
+    gather buffers over NVLink and arrival counters are bumped (``pa_decode_gather``)."""
     desc, kplane = _describe_cache(kv_cache)
     _require_cuda_or_pinned(query, "query")
     _require_cuda(block_tables, "block_tables")
@@ -347,12 +349,19 @@ def paged_attention_decode_batched(query: torch.Tensor, kv_cache: KvCacheArg, bl
     elif not workspace.is_cuda or workspace.numel() * workspace.element_size() < need:
         raise ValueError(f"workspace must be a CUDA tensor of at least {need} bytes")
     with _DeviceOf(kplane):
-        rc = lib.pa_decode(query.data_ptr(), query.stride(0), query.stride(1),
-                           out.data_ptr(), out.stride(0), out.stride(1),
-                           ctypes.byref(desc), block_tables.data_ptr(), block_tables.stride(0),
-                           seq_lens.data_ptr(), b, hq, workspace.data_ptr(),
-                           workspace.numel() * workspace.element_size(), _stream_ptr())
-    _lib.check(rc, "pa_decode")
+        if peers is None:
+            rc = lib.pa_decode(query.data_ptr(), query.stride(0), query.stride(1),
+                               out.data_ptr(), out.stride(0), out.stride(1),
+                               ctypes.byref(desc), block_tables.data_ptr(), block_tables.stride(0),
+                               seq_lens.data_ptr(), b, hq, workspace.data_ptr(),
+                               workspace.numel() * workspace.element_size(), _stream_ptr())
+        else:
+            rc = lib.pa_decode_gather(query.data_ptr(), query.stride(0), query.stride(1),
+                                      out.data_ptr(), out.stride(0), out.stride(1),
+                                      ctypes.byref(desc), block_tables.data_ptr(), block_tables.stride(0),
+                                      seq_lens.data_ptr(), b, hq, workspace.data_ptr(),
+                                      workspace.numel() * workspace.element_size(), ctypes.byref(peers), _stream_ptr())
+    _lib.check(rc, "pa_decode" if peers is None else "pa_decode_gather")
     return out
 
 

@@ -105,3 +105,129 @@ def gather_sequence_outputs(local_out: torch.Tensor, batch: int, world: int, ran
     dist.all_gather_into_tensor(buf.view(-1), pad.view(-1), group=group)
     parts = [buf[r, :len(shard_sequences(batch, world, r))] for r in range(world)]
     return torch.cat(parts, dim=0)
+
+
+class _DevMem:
+    """Raw device memory as a torch tensor (``__cuda_array_interface__``), no copy, no ownership."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+
+class PeerGather:
+    """KV-head-sharded decode with the output gather FUSED into the decode kernel.
+
+    ``HeadGather`` finishes the step with an NCCL all-gather: one more launch and a collective whose
+    latency (tens of microseconds through the host launch path) exceeds the kernel's at 8 GPUs.
+    Here every rank's gather buffer lives in peer-visible memory (``pa_peer_alloc`` + CUDA IPC, one
+    process per GPU); the decode kernel stores each finished output row into its own slot of EVERY
+    rank's buffer over NVLink and bumps its arrival counter there (``pa_decode_gather``); one tiny
+    ``pa_peer_wait`` kernel on the consumer's stream makes the gathered ``[world, B, Hq / world, D]``
+    visible.  Two buffer sets alternate (a fast rank may be one step ahead of a slow one; see
+    include/pa_b200.h).  ``torch.distributed`` is used only to exchange the 64-byte IPC handles.
+    """
+
+    def __init__(self, batch: int, num_q_heads: int, num_kv_heads: int, head_dim: int, device, world: Optional[int] = None,
+                 rank: Optional[int] = None, group=None, timeout_us: int = 2_000_000):
+        import ctypes
+
+        from . import _lib
+        self.group = group
+        self.world = world if world is not None else dist.get_world_size(group)
+        self.rank = rank if rank is not None else dist.get_rank(group)
+        if not (1 <= self.world <= 8):
+            raise ValueError("PeerGather supports 1..8 ranks of one node")
+        if num_kv_heads % self.world or num_q_heads % num_kv_heads:
+            raise ValueError("world must divide num_kv_heads, num_kv_heads must divide num_q_heads")
+        self.batch, self.num_q_heads, self.head_dim = batch, num_q_heads, head_dim
+        self.hq_local = num_q_heads // self.world
+        self.segments = batch * (num_kv_heads // self.world)          # arrivals per rank per step
+        self.device = torch.device(device)
+        self.timeout_us = timeout_us
+        self.step = 0
+        self._lib = _lib.load()
+        slot = batch * self.hq_local * head_dim * 2                    # bf16
+        self._set_bytes = self.world * slot
+        self._sig_off = (2 * self._set_bytes + 255) // 256 * 256
+        total = self._sig_off + 256
+        ptr, handle = ctypes.c_void_p(), ctypes.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.pa_peer_alloc(total, ctypes.byref(ptr), handle), "pa_peer_alloc")
+        self._base = ptr.value
+        handles = [None] * self.world
+        if self.world > 1:
+            dist.all_gather_object(handles, handle.raw, group=group)
+        self._remote = {}
+        for r in range(self.world):
+            if r == self.rank:
+                continue
+            rp = ctypes.c_void_p()
+            with torch.cuda.device(self.device):
+                _lib.check(self._lib.pa_peer_open(ctypes.create_string_buffer(handles[r], 64), ctypes.byref(rp)), "pa_peer_open")
+            self._remote[r] = rp.value
+        mem = torch.as_tensor(_DevMem(self._base, total), device=self.device)
+        self.sets = [mem[i * self._set_bytes:(i + 1) * self._set_bytes].view(torch.bfloat16)
+                     .view(self.world, batch, self.hq_local, head_dim) for i in range(2)]
+        self.sig = mem[self._sig_off:self._sig_off + 4 * self.world].view(torch.int32)
+        self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.epoch = torch.zeros(1, dtype=torch.int32, device=self.device)     # steps waited for, kept on the device
+        self._peers = []
+        for i in range(2):
+            pg = _lib.PaPeerGather()
+            pg.num_remote = self.world - 1
+            my_slot = i * self._set_bytes + self.rank * slot
+            for j, (r, base) in enumerate(sorted(self._remote.items())):
+                pg.remote_out[j] = base + my_slot
+                pg.remote_sig[j] = base + self._sig_off + 4 * self.rank
+            pg.local_sig = self._base + self._sig_off + 4 * self.rank
+            self._peers.append(pg)
+        if self.world > 1:
+            dist.barrier(group=group)                                   # every rank has mapped every buffer
+
+    def local_out(self) -> torch.Tensor:
+        """``[B, Hq / world, D]``: this rank's slot of the buffer set the NEXT ``decode`` fills."""
+        return self.sets[self.step % 2][self.rank]
+
+    def decode(self, query: torch.Tensor, kv_cache, block_tables: torch.Tensor, seq_lens: torch.Tensor,
+               workspace: Optional[torch.Tensor] = None, parity: Optional[int] = None) -> torch.Tensor:
+        """One head-sharded decode step on the current stream; returns the gathered outputs
+        ``[world, B, Hq / world, D]`` (valid for later work on this stream; use before the step after
+        next overwrites the set).  Both launches are graph-capturable (the step number the wait needs
+        lives on the device): capture one graph per ``parity`` (0, 1) and replay them ALTERNATELY,
+        starting with 0 - all ranks must run the same sequence of steps."""
+        from . import _lib
+        from . import paged_attention as P
+        i = self.step % 2 if parity is None else parity
+        P.paged_attention_decode_batched(query, kv_cache, block_tables, seq_lens, out=self.sets[i][self.rank],
+                                         workspace=workspace, peers=self._peers[i])
+        if parity is None:
+            self.step += 1
+        with torch.cuda.device(self.device):
+            rc = self._lib.pa_peer_wait_next(self.sig.data_ptr(), self.world, self.epoch.data_ptr(), self.segments,
+                                             self.timeout_us, self.status.data_ptr(),
+                                             torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "pa_peer_wait_next")
+        return self.sets[i]
+
+    def check(self) -> None:
+        """Synchronises and raises if a wait timed out (a peer never delivered its rows)."""
+        late = int(self.status.item())
+        if late:
+            raise RuntimeError(f"PeerGather: rank {late - 1} did not deliver its outputs within {self.timeout_us} us")
+
+    def full(self, gathered: torch.Tensor) -> torch.Tensor:
+        """``[B, Hq, D]`` with heads in global order (one small copy)."""
+        return gathered.permute(1, 0, 2, 3).reshape(self.batch, self.num_q_heads, self.head_dim)
+
+    def close(self) -> None:
+        if self._base is None:
+            return
+        torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            dist.barrier(group=self.group)                              # nobody is still writing into a peer
+        self.sets, self.sig = [], None
+        with torch.cuda.device(self.device):
+            for base in self._remote.values():
+                self._lib.pa_peer_close(base)
+            self._lib.pa_peer_free(self._base)
+        self._remote, self._base = {}, None
