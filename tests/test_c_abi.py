@@ -1,0 +1,63 @@
+"""The C-ABI boundary without a GPU: libpa_b200.so builds / loads, exports every function
+include/pa_b200.h declares, the ctypes table binds exactly that set, and argument validation
+returns status codes (no compute call is made here)."""
+import ctypes
+import os
+import re
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from vllm_from_scratch_b200 import _lib  # noqa: E402
+from vllm_from_scratch_b200.build import build_library  # noqa: E402
+
+HEADER = os.path.join(ROOT, "include", "pa_b200.h")
+
+
+def declared_functions():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"^\s*(?:int|size_t|const char\*)\s+(pa_[a-z0-9_]+)\s*\(", src, flags=re.M)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return ctypes.CDLL(build_library())
+
+
+def test_header_declares_the_expected_entry_points():
+    names = declared_functions()
+    for must in ("pa_decode", "pa_decode_gather", "pa_reshape_and_cache", "pa_slot_mapping", "pa_copy_blocks",
+                 "pa_swap_blocks", "pa_swap_blocks_staged", "pa_prefill", "pa_prefill_varlen", "pa_rope_and_cache",
+                 "pa_peer_wait", "pa_peer_wait_next", "pa_decode_workspace_bytes"):
+        assert must in names, must
+
+
+def test_library_exports_every_declared_symbol(lib):
+    for name in declared_functions():
+        assert hasattr(lib, name), f"{name} is declared in include/pa_b200.h but not exported"
+
+
+def test_ctypes_table_binds_exactly_the_declared_set():
+    assert sorted(_lib.SIGNATURES) == declared_functions()
+
+
+def test_struct_mirrors_have_the_c_layout():
+    assert ctypes.sizeof(_lib.PaKvCache) == 2 * 8 + 3 * 8 + 6 * 4
+    assert ctypes.sizeof(_lib.PaPeerGather) == 8 + 7 * 8 + 7 * 8 + 8            # int32 + padding, 2 x 7 pointers, pointer
+
+
+def test_status_strings_and_argument_validation_without_a_gpu(lib):
+    lib.pa_status_string.restype = ctypes.c_char_p
+    assert lib.pa_abi_version() >= 1
+    assert lib.pa_status_string(0) == b"ok" or lib.pa_status_string(0)
+    # null / malformed arguments come back as negative status codes, never as a crash or an exception
+    assert lib.pa_copy_blocks(None, 0, 1, 0, 16, None, 1, None) < 0
+    assert lib.pa_swap_blocks(None, 0, 0, None, 0, 0, 1, 16, None, 1, 0, None) < 0
+    assert lib.pa_slot_mapping(None, 0, 4, 16, None, None) < 0
+    assert lib.pa_peer_wait(None, 2, 0, 10, None, None) < 0
+    assert lib.pa_decode_gather(None, 0, 0, None, 0, 0, None, None, 0, None, 1, 1, None, 0, None, None) < 0
+    # empty work is a no-op success
+    assert lib.pa_copy_blocks(None, 0, 0, 0, 0, None, 0, None) == 0
