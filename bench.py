@@ -57,7 +57,7 @@ def parse_args():
                     help="N > 1: 'seq' = every rank its own sequences (weak scaling, no collective); 'head' = "
                          "every rank Hkv / N KV heads of the SAME batch + one NCCL all-gather of the outputs "
                          "(strong scaling; default workload c3)")
-    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+    ap.add_argument("--gather", default="peer", choices=["peer", "peer-counter", "nccl"],
                     help="--shard head: 'peer' = output gather fused into the decode kernel over NVLink peer memory "
                          "(default); 'nccl' = decode kernel + one NCCL all-gather")
     ap.add_argument("--layers", type=int, default=0, help="per-layer caches the loop rotates over")
@@ -238,16 +238,17 @@ def run_ours(args):
         hkv, hq = len(S.shard_kv_heads(hkv, world, rank)), len(S.shard_q_heads(hq, hkv, world, rank))
         hkv_full = wl[3]
         wl = (b, ctx, hq, hkv, d, bs, def_layers, desc)
-        if args.gather == "peer":
+        if args.gather.startswith("peer"):
             # output gather fused into the decode kernel: rows go to every rank's buffer over NVLink
             # peer memory, arrival counters instead of a collective (sharding.PeerGather)
-            gather = S.PeerGather(b, hq_full, hkv_full, d, dev, world=world, rank=rank)
+            gather = S.PeerGather(b, hq_full, hkv_full, d, dev, world=world, rank=rank,
+                                  protocol="counter" if args.gather == "peer-counter" else "ll")
         else:
             gather = S.HeadGather(b, hq_full, d, torch.bfloat16, dev, world=world, rank=rank)
     pool, bts_h, lens_h, q_h, k_h, v_h, slots_h = make_workload(torch, dev, wl, layers,
                                                                 seed=1234 + (0 if head_mode else rank))
     bts, lens, q = bts_h.to(dev), lens_h.to(dev), q_h.to(dev)
-    peer_mode = head_mode and args.gather == "peer"
+    peer_mode = head_mode and args.gather.startswith("peer")
     out = gather.local_out() if head_mode else torch.empty_like(q)
     ws = P.new_decode_workspace(b, hq, hkv, d, dev)
     caches = [pool.layer(i) for i in range(layers)]
@@ -413,8 +414,10 @@ def run_ours(args):
                    "head_dim": d, "block_size": bs, "kv_layout": "[2, L, NB, Hkv, BS, D] (reference pool)",
                    "block_tables": "seeded randperm, fully scattered",
                    "parallelism": (f"KV-head-sharded x{world}: {hkv} KV / {hq} Q heads per GPU, " +
-                                   ("output gather fused into the decode kernel (NVLink peer stores + arrival "
-                                    "counters, no collective call)" if peer_mode else
+                                   ("output gather fused into the decode kernel (NVLink peer stores, " +
+                                    ("fence + arrival counters" if args.gather == "peer-counter" else
+                                     "LL protocol: step number in every 8-byte word, no fence") +
+                                    ", no collective call)" if peer_mode else
                                     f"one NCCL all-gather of [B, Hq/{world}, D] per step") if head_mode else
                                    f"sequence-sharded x{world}, one pool per GPU, no collective"),
                    "l2": f"inputs larger than L2: loop rotates over {layers} per-layer caches of "

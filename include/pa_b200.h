@@ -122,6 +122,13 @@ typedef struct {
   void* remote_out[PA_MAX_REMOTE_PEERS];
   uint32_t* remote_sig[PA_MAX_REMOTE_PEERS];
   uint32_t* local_sig;
+  /* LL ("flag in data") form, selected by a non-null ll_epoch: remote_out[r] then
+   * point at 8-byte-word areas (2x the slot size) and every 4-byte output word
+   * travels as {data, step number} in ONE 8-byte store - nothing is fenced or
+   * counted on the sender (remote_sig / local_sig unused).  *ll_epoch (device
+   * uint32) holds the number of completed steps; pa_peer_unpack advances it.
+   * `out` must be a contiguous [B, Hq, D] slot.                               */
+  const uint32_t* ll_epoch;
 } PaPeerGather;
 
 int pa_decode_gather(const void* q, int64_t q_stride_b, int64_t q_stride_h,
@@ -146,6 +153,17 @@ int pa_peer_wait(const uint32_t* local_sig, int32_t world, uint32_t expected,
 int pa_peer_wait_next(const uint32_t* local_sig, int32_t world, uint32_t* epoch,
                       uint32_t segments, int64_t timeout_us, int32_t* status,
                       void* stream);
+
+/* Receiver side of the LL form, on the consumer's stream after pa_decode_gather:
+ * polls every 8-byte word the remote ranks stored into this rank's LL area
+ * ([world][words_per_slot] x {data, flag}) until its flag is *epoch + 1, writes the
+ * data words into `gathered` ([world][words_per_slot] uint32; the local slot is
+ * left alone - the decode kernel wrote it in place), then advances *epoch.
+ * `done` is a zero-initialised device word (block counter).  Bounded like
+ * pa_peer_wait.  Graph-capturable (no per-step host argument).                */
+int pa_peer_unpack(const void* ll_local, void* gathered, int32_t world, int32_t rank,
+                   int32_t words_per_slot, uint32_t* epoch, uint32_t* done,
+                   int64_t timeout_us, int32_t* status, void* stream);
 
 /* Peer-visible device memory for the gather buffers and counters (the one place
  * the library allocates: cudaMalloc, zero-filled, plus its 64-byte CUDA IPC

@@ -31,7 +31,7 @@ def test_header_declares_the_expected_entry_points():
     names = declared_functions()
     for must in ("pa_decode", "pa_decode_gather", "pa_reshape_and_cache", "pa_slot_mapping", "pa_copy_blocks",
                  "pa_swap_blocks", "pa_swap_blocks_staged", "pa_prefill", "pa_prefill_varlen", "pa_rope_and_cache",
-                 "pa_peer_wait", "pa_peer_wait_next", "pa_decode_workspace_bytes"):
+                 "pa_peer_wait", "pa_peer_wait_next", "pa_peer_unpack", "pa_decode_workspace_bytes"):
         assert must in names, must
 
 
@@ -46,7 +46,7 @@ def test_ctypes_table_binds_exactly_the_declared_set():
 
 def test_struct_mirrors_have_the_c_layout():
     assert ctypes.sizeof(_lib.PaKvCache) == 2 * 8 + 3 * 8 + 6 * 4
-    assert ctypes.sizeof(_lib.PaPeerGather) == 8 + 7 * 8 + 7 * 8 + 8            # int32 + padding, 2 x 7 pointers, pointer
+    assert ctypes.sizeof(_lib.PaPeerGather) == 8 + 7 * 8 + 7 * 8 + 8 + 8        # int32 + padding, 2 x 7 pointers, 2 pointers
 
 
 def test_status_strings_and_argument_validation_without_a_gpu(lib):

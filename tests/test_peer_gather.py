@@ -36,20 +36,23 @@ def _case(lens, hq=32, hkv=8, d=128, bs=16, seed=0):
     return q, kv, bts.to(DEV), lens.to(DEV)
 
 
+@pytest.mark.parametrize("protocol", ["counter", "ll"])
 @pytest.mark.parametrize("lens", [[2048] * 16, [0, 1, 17, 5000, 0, 333, 40000, 16], [100] * 3], ids=["whole", "mixed", "short"])
-def test_world1_fused_gather_counts_segments_and_matches_plain_decode(lens):
+def test_world1_fused_gather_counts_segments_and_matches_plain_decode(lens, protocol):
     from vllm_from_scratch_b200 import paged_attention as P
     from vllm_from_scratch_b200 import sharding as S
     q, kv, bts, sl = _case(lens)
     want = P.paged_attention_decode_batched(q, kv, bts, sl)
-    pg = S.PeerGather(len(lens), 32, 8, 128, DEV, world=1, rank=0, timeout_us=500_000)
+    pg = S.PeerGather(len(lens), 32, 8, 128, DEV, world=1, rank=0, timeout_us=500_000, protocol=protocol)
     try:
         for step in range(1, 4):
             got = pg.decode(q, kv, bts, sl)
             assert got.shape == (1, len(lens), 32, 128)
             assert torch.equal(pg.full(got), want), f"step {step}"
             pg.check()                                        # no timeout: every segment was counted
-            assert int(pg.sig[0].item()) == step * len(lens) * 8
+            if protocol == "counter":
+                assert int(pg.sig[0].item()) == step * len(lens) * 8
+            assert int(pg.epoch.item()) == step                # the step number advanced on the device
         assert pg.local_out().data_ptr() != got[0].data_ptr()   # the two buffer sets alternate
     finally:
         pg.close()
@@ -88,3 +91,37 @@ def test_gather_refuses_shapes_outside_the_fast_path():
     pg.local_sig = sig.data_ptr()
     with pytest.raises(RuntimeError, match="pa_decode_gather"):
         P.paged_attention_decode_batched(q, kv, bts, sl, peers=pg)
+
+
+def test_ll_unpack_polls_flags_and_times_out():
+    """pa_peer_unpack on hand-made LL words: a 'remote' slot whose words carry this step's flag is
+    unpacked; a word with a stale flag makes the kernel give up after the timeout and name the rank."""
+    from vllm_from_scratch_b200 import _lib
+    lib = _lib.load()
+    world, rank, words = 3, 1, 1000
+    g = torch.Generator().manual_seed(3)
+    data = torch.randint(-2**31, 2**31 - 1, (world, words), generator=g, dtype=torch.int64).to(torch.int32)
+    ll = torch.zeros(world, words, 2, dtype=torch.int32)
+    ll[:, :, 0] = data
+    ll[:, :, 1] = 5                                           # flag of step 5 = epoch 4 + 1
+    ll[rank] = -1                                             # the local LL slot is never read
+    ll_d = ll.to(DEV)
+    gathered = torch.full((world, words), 77, dtype=torch.int32, device=DEV)
+    epoch = torch.tensor([4], dtype=torch.int32, device=DEV)
+    done = torch.zeros(1, dtype=torch.int32, device=DEV)
+    status = torch.zeros(1, dtype=torch.int32, device=DEV)
+    st = torch.cuda.current_stream().cuda_stream
+    _lib.check(lib.pa_peer_unpack(ll_d.data_ptr(), gathered.data_ptr(), world, rank, words, epoch.data_ptr(),
+                                  done.data_ptr(), 200_000, status.data_ptr(), st), "pa_peer_unpack")
+    torch.cuda.synchronize()
+    assert int(status.item()) == 0 and int(epoch.item()) == 5 and int(done.item()) == 0
+    got = gathered.cpu()
+    assert torch.equal(got[0], data[0]) and torch.equal(got[2], data[2])
+    assert (got[rank] == 77).all()                            # local slot untouched
+    # next step: rank 2's word 10 still carries the old flag -> bounded wait, status names rank 2
+    ll_d[:, :, 1] = 6
+    ll_d[2, 10, 1] = 5
+    _lib.check(lib.pa_peer_unpack(ll_d.data_ptr(), gathered.data_ptr(), world, rank, words, epoch.data_ptr(),
+                                  done.data_ptr(), 3000, status.data_ptr(), st), "pa_peer_unpack")
+    torch.cuda.synchronize()
+    assert int(status.item()) == 3

@@ -38,21 +38,22 @@ def main():
     bts, sl = bts.to(dev), sl.to(dev)
     kvh, qh = S.shard_kv_heads(hkv, world, rank), S.shard_q_heads(hq, hkv, world, rank)
     kv_local = kv[:, :, kvh.start:kvh.stop].contiguous()
-    pg = S.PeerGather(len(lens), hq, hkv, d, dev, world=world, rank=rank, timeout_us=5_000_000)
     ok = True
-    for step in range(6):
-        q = torch.randn(len(lens), hq, d, generator=g).to(torch.bfloat16).to(dev)     # same on every rank
-        want = P.paged_attention_decode_batched(q, kv, bts, sl)
-        time.sleep(0.002 * ((rank + step) % world))                                   # let the ranks drift
-        got = pg.full(pg.decode(q[:, qh.start:qh.stop].contiguous(), kv_local, bts, sl))
-        pg.check()
-        # split-K unit boundaries depend on the number of local heads, so merge order (not values) differs
-        same = (got.float() - want.float()).abs().max().item() <= 1e-2
-        ok &= same
-        if not same:
-            print(f"rank {rank} step {step}: max diff {(got.float() - want.float()).abs().max().item()}", flush=True)
+    for protocol in ("ll", "counter"):
+        pg = S.PeerGather(len(lens), hq, hkv, d, dev, world=world, rank=rank, timeout_us=5_000_000, protocol=protocol)
+        for step in range(6):
+            q = torch.randn(len(lens), hq, d, generator=g).to(torch.bfloat16).to(dev)     # same on every rank
+            want = P.paged_attention_decode_batched(q, kv, bts, sl)
+            time.sleep(0.002 * ((rank + step) % world))                                   # let the ranks drift
+            got = pg.full(pg.decode(q[:, qh.start:qh.stop].contiguous(), kv_local, bts, sl))
+            pg.check()
+            # split-K unit boundaries depend on the number of local heads, so merge order (not values) differs
+            err = (got.float() - want.float()).abs().max().item()
+            ok &= err <= 1e-2
+            if err > 1e-2:
+                print(f"rank {rank} {protocol} step {step}: max diff {err}", flush=True)
+        pg.close()
     print(f"peer_gather_check rank {rank}/{world}: {'OK' if ok else 'MISMATCH'}", flush=True)
-    pg.close()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 

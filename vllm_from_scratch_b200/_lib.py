@@ -39,6 +39,7 @@ class PaPeerGather(Structure):
         ("remote_out", c_void_p * 7),
         ("remote_sig", c_void_p * 7),
         ("local_sig", c_void_p),
+        ("ll_epoch", c_void_p),
     ]
 
 
@@ -57,6 +58,8 @@ SIGNATURES = {
                                  POINTER(PaPeerGather), c_void_p]),
     "pa_peer_wait": (c_int, [c_void_p, c_int32, ctypes.c_uint32, c_int64, c_void_p, c_void_p]),
     "pa_peer_wait_next": (c_int, [c_void_p, c_int32, c_void_p, ctypes.c_uint32, c_int64, c_void_p, c_void_p]),
+    "pa_peer_unpack": (c_int, [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p, c_int64,
+                               c_void_p, c_void_p]),
     "pa_peer_alloc": (c_int, [c_size_t, POINTER(c_void_p), c_void_p]),
     "pa_peer_open": (c_int, [c_void_p, POINTER(c_void_p)]),
     "pa_peer_close": (c_int, [c_void_p]),

@@ -161,16 +161,22 @@ static int decode_impl(const void* q, int64_t q_stride_b, int64_t q_stride_h, vo
   p.num_remote = 0;
   p.local_sig = nullptr;
   for (int r = 0; r < 7; ++r) { p.remote_out[r] = nullptr; p.remote_sig[r] = nullptr; }
+  p.ll_epoch = nullptr;
   if (peers) {
-    if (peers->num_remote < 0 || peers->num_remote > 7 || !peers->local_sig) return PA_ERR_BAD_ARG;
+    const bool ll = peers->ll_epoch != nullptr;            // LL form: flags travel with the data, no counters
+    if (peers->num_remote < 0 || peers->num_remote > 7 || (!ll && !peers->local_sig)) return PA_ERR_BAD_ARG;
     for (int r = 0; r < peers->num_remote; ++r) {
-      if (!peers->remote_out[r] || !peers->remote_sig[r]) return PA_ERR_BAD_ARG;
-      if (reinterpret_cast<uintptr_t>(peers->remote_out[r]) & 3) return PA_ERR_MISALIGNED;
+      if (!peers->remote_out[r] || (!ll && !peers->remote_sig[r])) return PA_ERR_BAD_ARG;
+      if (reinterpret_cast<uintptr_t>(peers->remote_out[r]) & (ll ? 7 : 3)) return PA_ERR_MISALIGNED;
       p.remote_out[r] = peers->remote_out[r];
-      p.remote_sig[r] = peers->remote_sig[r];
+      p.remote_sig[r] = ll ? nullptr : peers->remote_sig[r];
     }
     p.num_remote = peers->num_remote;
-    p.local_sig = peers->local_sig;
+    p.local_sig = ll ? nullptr : peers->local_sig;
+    p.ll_epoch = peers->ll_epoch;
+    // the LL word of an output word is addressed by the word's offset in a CONTIGUOUS [B, Hq, D] slot
+    if (ll && (o_stride_h != cache->head_dim || o_stride_b != (int64_t)num_q_heads * cache->head_dim))
+      return PA_ERR_BAD_ARG;
   }
   p.q = q; p.out = out; p.k = cache->k; p.v = cache->v;
   p.block_tables = block_tables; p.seq_lens = seq_lens;
@@ -295,6 +301,63 @@ extern "C" int pa_peer_wait_next(const uint32_t* local_sig, int32_t world, uint3
   if (!local_sig || !epoch || world < 1 || world > 8 || timeout_us <= 0) return PA_ERR_BAD_ARG;
   pa_peer_wait_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(
       local_sig, world, 0u, (unsigned long long)timeout_us * 1000ull, status, epoch, segments);
+  return cudaGetLastError() == cudaSuccess ? PA_OK : PA_ERR_CUDA;
+}
+
+namespace {
+// Receiver side of the LL gather: every 8-byte word {data, flag} that a remote rank stored into this
+// rank's LL area is polled until its flag equals this step's number, and its data word is written
+// into the gather set.  The last block to finish advances the step number.  Bounded like the wait.
+__global__ void __launch_bounds__(256)
+pa_peer_unpack_kernel(const uint2* ll, uint32_t* gathered, int world, int rank, int words, uint32_t* epoch,
+                      uint32_t* done, unsigned long long timeout_ns, int32_t* status) {
+  const uint32_t flag = *reinterpret_cast<volatile uint32_t*>(epoch) + 1u;
+  const int total = world * words;
+  bool dead = status && *reinterpret_cast<volatile int32_t*>(status) != 0;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int r = i / words;
+    if (r == rank) continue;                               // the local slot was written in place by the decode kernel
+    uint2 v;
+    for (unsigned spin = 0;; ++spin) {
+      asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(ll + i) : "memory");
+      if (v.y == flag || dead) break;
+      if ((spin & 255u) == 255u) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        if (t - t0 > timeout_ns) {
+          if (status) atomicExch(status, 1 + r);
+          dead = true;
+        }
+      }
+    }
+    gathered[i] = v.x;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(done, 1u) == gridDim.x - 1) {
+      *done = 0u;
+      *epoch = flag;
+    }
+  }
+}
+}  // namespace
+
+extern "C" int pa_peer_unpack(const void* ll_local, void* gathered, int32_t world, int32_t rank, int32_t words_per_slot,
+                              uint32_t* epoch, uint32_t* done, int64_t timeout_us, int32_t* status, void* stream) {
+  if (!ll_local || !gathered || !epoch || !done || world < 1 || world > 8 || rank < 0 || rank >= world ||
+      words_per_slot <= 0 || timeout_us <= 0)
+    return PA_ERR_BAD_ARG;
+  if ((reinterpret_cast<uintptr_t>(ll_local) & 7) || (reinterpret_cast<uintptr_t>(gathered) & 3)) return PA_ERR_MISALIGNED;
+  const int64_t total = (int64_t)world * words_per_slot;
+  if (total > 0x7fffffff) return PA_ERR_UNSUPPORTED;
+  int blocks = (int)((total + 256 * 8 - 1) / (256 * 8));   // ~8 words per thread
+  if (blocks > 64) blocks = 64;
+  pa_peer_unpack_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint2*>(ll_local), static_cast<uint32_t*>(gathered), world, rank, words_per_slot, epoch, done,
+      (unsigned long long)timeout_us * 1000ull, status);
   return cudaGetLastError() == cudaSuccess ? PA_OK : PA_ERR_CUDA;
 }
 

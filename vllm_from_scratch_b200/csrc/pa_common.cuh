@@ -59,6 +59,10 @@ struct PaDecodeParams {
   void* remote_out[7];
   uint32_t* remote_sig[7];
   uint32_t* local_sig;    // null = no signalling
+  // LL ("flag in data") form of the same gather: when ll_epoch is set, remote_out[r] are 8-byte-word
+  // buffers - every 4-byte output word travels as {data, step number} in ONE 8-byte store - and nothing
+  // is fenced or counted on the sender; the receiver's unpack kernel polls the step numbers
+  const uint32_t* ll_epoch;   // device word holding the number of completed steps; this step's flag = *ll_epoch + 1
 };
 
 struct PaCursor {

@@ -239,6 +239,16 @@ __device__ __forceinline__ void build_plan(const int32_t* __restrict__ seq_lens,
 // Replicate a final 4-byte output store into this rank's slot of every remote gather buffer
 // (plain stores over NVLink: fire and forget).
 __device__ __forceinline__ void peer_store32(const PaDecodeParams& p, int64_t off_elems, uint32_t v) {
+  if (p.num_remote == 0) return;
+  if (p.ll_epoch) {
+    // this step's flag (never 0); loaded where it is used - output stores are rare - instead of
+    // living in a register of every warp for the whole kernel
+    const uint32_t ll_flag = __ldg(p.ll_epoch) + 1u;
+    // LL: {data, flag} as one 8-byte store (single NVLink write, never torn); word index = off_elems / 2
+    for (int r = 0; r < p.num_remote; ++r)
+      *reinterpret_cast<uint2*>(static_cast<uint8_t*>(p.remote_out[r]) + off_elems * 4) = make_uint2(v, ll_flag);
+    return;
+  }
   for (int r = 0; r < p.num_remote; ++r)
     *reinterpret_cast<uint32_t*>(static_cast<__nv_bfloat16*>(p.remote_out[r]) + off_elems) = v;
 }

@@ -124,11 +124,14 @@ class PeerGather:
     rank's buffer over NVLink and bumps its arrival counter there (``pa_decode_gather``); one tiny
     ``pa_peer_wait`` kernel on the consumer's stream makes the gathered ``[world, B, Hq / world, D]``
     visible.  Two buffer sets alternate (a fast rank may be one step ahead of a slow one; see
-    include/pa_b200.h).  ``torch.distributed`` is used only to exchange the 64-byte IPC handles.
+    include/pa_b200.h).  Default ``protocol='ll'``: every 4-byte output word travels as {data, step
+    number} in one 8-byte store into an LL area of the receiver, the sender fences and counts nothing,
+    and the receiver's ``pa_peer_unpack`` kernel polls the step numbers and fills the gather set;
+    ``'counter'`` is the plain-stores + ``fence.sys`` + arrival-counter form.  ``torch.distributed`` is used only to exchange the 64-byte IPC handles.
     """
 
     def __init__(self, batch: int, num_q_heads: int, num_kv_heads: int, head_dim: int, device, world: Optional[int] = None,
-                 rank: Optional[int] = None, group=None, timeout_us: int = 2_000_000):
+                 rank: Optional[int] = None, group=None, timeout_us: int = 2_000_000, protocol: str = "ll"):
         import ctypes
 
         from . import _lib
@@ -147,8 +150,15 @@ class PeerGather:
         self.step = 0
         self._lib = _lib.load()
         slot = batch * self.hq_local * head_dim * 2                    # bf16
+        if protocol not in ("ll", "counter"):
+            raise ValueError("protocol must be 'll' (flag travels with every data word, nothing fenced on the sender) "
+                             "or 'counter' (plain stores + fence + arrival counters)")
+        self.protocol = protocol
+        self._slot_words = slot // 4
         self._set_bytes = self.world * slot
-        self._sig_off = (2 * self._set_bytes + 255) // 256 * 256
+        self._ll_off = (2 * self._set_bytes + 255) // 256 * 256         # LL areas: 8 bytes per 4-byte output word
+        self._ll_set_bytes = 2 * self._set_bytes
+        self._sig_off = (self._ll_off + 2 * self._ll_set_bytes + 255) // 256 * 256
         total = self._sig_off + 256
         ptr, handle = ctypes.c_void_p(), ctypes.create_string_buffer(64)
         with torch.cuda.device(self.device):
@@ -171,15 +181,22 @@ class PeerGather:
         self.sig = mem[self._sig_off:self._sig_off + 4 * self.world].view(torch.int32)
         self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.epoch = torch.zeros(1, dtype=torch.int32, device=self.device)     # steps waited for, kept on the device
+        self._done = torch.zeros(1, dtype=torch.int32, device=self.device)     # block counter of the unpack kernel
         self._peers = []
         for i in range(2):
             pg = _lib.PaPeerGather()
             pg.num_remote = self.world - 1
             my_slot = i * self._set_bytes + self.rank * slot
             for j, (r, base) in enumerate(sorted(self._remote.items())):
-                pg.remote_out[j] = base + my_slot
-                pg.remote_sig[j] = base + self._sig_off + 4 * self.rank
-            pg.local_sig = self._base + self._sig_off + 4 * self.rank
+                if protocol == "ll":
+                    pg.remote_out[j] = base + self._ll_off + i * self._ll_set_bytes + self.rank * slot * 2
+                else:
+                    pg.remote_out[j] = base + my_slot
+                    pg.remote_sig[j] = base + self._sig_off + 4 * self.rank
+            if protocol == "ll":
+                pg.ll_epoch = self.epoch.data_ptr()
+            else:
+                pg.local_sig = self._base + self._sig_off + 4 * self.rank
             self._peers.append(pg)
         if self.world > 1:
             dist.barrier(group=group)                                   # every rank has mapped every buffer
@@ -203,10 +220,15 @@ class PeerGather:
         if parity is None:
             self.step += 1
         with torch.cuda.device(self.device):
-            rc = self._lib.pa_peer_wait_next(self.sig.data_ptr(), self.world, self.epoch.data_ptr(), self.segments,
-                                             self.timeout_us, self.status.data_ptr(),
-                                             torch.cuda.current_stream().cuda_stream)
-        _lib.check(rc, "pa_peer_wait_next")
+            st = torch.cuda.current_stream().cuda_stream
+            if self.protocol == "ll":
+                rc = self._lib.pa_peer_unpack(self._base + self._ll_off + i * self._ll_set_bytes, self.sets[i].data_ptr(),
+                                              self.world, self.rank, self._slot_words, self.epoch.data_ptr(),
+                                              self._done.data_ptr(), self.timeout_us, self.status.data_ptr(), st)
+            else:
+                rc = self._lib.pa_peer_wait_next(self.sig.data_ptr(), self.world, self.epoch.data_ptr(), self.segments,
+                                                 self.timeout_us, self.status.data_ptr(), st)
+        _lib.check(rc, "pa_peer_unpack" if self.protocol == "ll" else "pa_peer_wait_next")
         return self.sets[i]
 
     def check(self) -> None:
