@@ -355,6 +355,45 @@ def test_c3_long_context_8x32k_properties(P):
     assert (sub.float() - out[2:5].float()).abs().max().item() <= 2e-2
 
 
+def test_c5_shard_64x8k_properties(P):
+    # BASELINE.json configs[4], one GPU's shard of 512 x 8k over 8 GPUs: 64 seqs x 8192, ragged tail.
+    q, kv, bts, lens = _full_case(64, 8192 - 300, 8192, seed=11, nb_spare=16)
+    lens_d, bts_d = lens.to(DEV), bts.to(DEV)
+    out = P.paged_attention_decode_batched(q, kv, bts_d, lens_d)
+    kv_c = kv.cpu()
+    for i in (0, 31, 63):                                      # oracle on sampled sequences
+        ref = O.decode_vectorised(q[i].cpu(), kv_c, bts[i].tolist(), int(lens[i]), 128, 32, 8, 16,
+                                  compute_dtype=torch.float32)
+        assert (out[i].float().cpu() - ref).abs().max().item() <= 2e-2
+    assert torch.equal(out, P.paged_attention_decode_batched(q, kv, bts_d, lens_d))       # reproducible bits
+    # linearity in V: attention weights do not depend on V, so out(V) + out(V') == out(V + V') up to bf16 rounding
+    kv_b = kv.clone()
+    kv_b[1] = torch.randn(kv[1].shape, generator=torch.Generator(device=DEV).manual_seed(12), device=DEV).to(torch.bfloat16)
+    kv_sum = kv.clone()
+    kv_sum[1] = (kv[1].float() + kv_b[1].float()).to(torch.bfloat16)
+    out_b = P.paged_attention_decode_batched(q, kv_b, bts_d, lens_d)
+    out_sum = P.paged_attention_decode_batched(q, kv_sum, bts_d, lens_d)
+    assert (out_sum.float() - (out.float() + out_b.float())).abs().max().item() <= 3e-2
+    # a sequence's result does not depend on its neighbours in the batch (tolerance: split points move)
+    one = P.paged_attention_decode_batched(q[40:41], kv, bts_d[40:41], lens_d[40:41])
+    assert (one.float() - out[40:41].float()).abs().max().item() <= 2e-2
+
+
+@pytest.mark.parametrize("hkv", [1, 2, 4])
+def test_head_shard_rank_shapes_vs_oracle(P, hkv):
+    # per-rank shapes of KV-head-sharded 32k decode (Hkv / P heads): few, very long segments - the
+    # split-K plan caps the partials per segment (kMaxPartials), every head must still match the oracle
+    hq = 4 * hkv
+    q, kv, bts, lens = _full_case(3, 32768 - 77, 32768, seed=20 + hkv, nb_spare=8, hq=hq, hkv=hkv)
+    out = P.paged_attention_decode_batched(q, kv, bts.to(DEV), lens.to(DEV))
+    kv_c = kv.cpu()
+    for i in range(3):
+        ref = O.decode_vectorised(q[i].cpu(), kv_c, bts[i].tolist(), int(lens[i]), 128, hq, hkv, 16,
+                                  compute_dtype=torch.float32)
+        assert (out[i].float().cpu() - ref).abs().max().item() <= 2e-2
+    assert torch.equal(out, P.paged_attention_decode_batched(q, kv, bts.to(DEV), lens.to(DEV)))
+
+
 def test_constant_v_property(P):
     # softmax weights sum to one: with V == c everywhere the output is c (any split-K plan)
     q, kv, bts, lens = _full_case(16, 100, 5000, seed=3)
