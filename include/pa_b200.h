@@ -284,7 +284,9 @@ int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
  * token.  cu_q_lens int32 [batch + 1], ctx_lens int32 [batch] on the DEVICE;
  * max_q_len (host) >= every q_len sizes the grid.  Tensor-core path only:
  * PA_ERR_UNSUPPORTED for shapes outside it (see pa_prefill); the caller then
- * loops pa_prefill per sequence.                                              */
+ * loops pa_prefill per sequence.                                              
+ * A request with ctx_lens[s] < its q_len (e.g. ctx_lens[s] = 0) is skipped and
+ * its rows of `out` are left alone: callers mask requests out that way.        */
 int pa_prefill_varlen(const void* q, int64_t q_stride_t, int64_t q_stride_h,
                       void* out, int64_t o_stride_t, int64_t o_stride_h,
                       const PaKvCache* cache,

@@ -290,3 +290,44 @@ def test_tiny_engine_cuda_bf16_varlen_one_launch():
     b, rb = _run_tiny("cuda", TwoKernel, **cfg)
     same = sum(x.output_token_ids == y.output_token_ids for x, y in zip(ra, rb))
     assert same >= len(ra) // 2, (same, len(ra))    # greedy tokens of a random-init bf16 model may flip on ties
+
+
+@pytest.mark.gpu
+def test_tiny_engine_cuda_bf16_split_route_for_decode_heavy_mixed_steps(monkeypatch):
+    """Mixed steps whose decode requests stream a lot of KV go: decode rows -> decode kernel, prefill
+    chunks -> the same varlen launch with the decode requests masked out (ctx 0).  Forced here with a
+    zero threshold; every row of the step must match the one-launch route within the bf16 tolerance."""
+    from vllm_from_scratch_b200 import paged_attention as P
+    seen = {"split": 0, "err": 0.0}
+
+    class Checked:
+        reshape_and_cache = staticmethod(P.reshape_and_cache)
+        prefill_tensor_core_available = staticmethod(P.prefill_tensor_core_available)
+        paged_attention_decode_batched = staticmethod(P.paged_attention_decode_batched)
+
+        @staticmethod
+        def paged_attention_prefill_varlen(q, cache, bts, cu, ctx, max_q, out=None):
+            res = P.paged_attention_prefill_varlen(q, cache, bts, cu, ctx, max_q, out=out)
+            if out is not None:                              # split route: decode requests are masked out
+                seen["split"] += 1
+                assert int((ctx == 0).sum()) > 0
+                Checked.pending = (q, cache, bts, cu, max_q, res)
+            return res
+
+    orig_attend = engine_adapter._attend
+
+    def attend(attn, ops, md, q, cache, t, h, d):
+        y = orig_attend(attn, ops, md, q, cache, t, h, d)
+        if getattr(Checked, "pending", None) is not None:
+            qq, cc, bts, cu, max_q, out = Checked.pending
+            Checked.pending = None
+            full = P.paged_attention_prefill_varlen(qq, cc, bts, cu, md.ctx_lens, max_q)     # one-launch route
+            seen["err"] = max(seen["err"], (full.float() - out.float()).abs().max().item())
+        return y
+
+    monkeypatch.setattr(engine_adapter, "_attend", attend)
+    monkeypatch.setattr(engine_adapter, "SPLIT_DECODE_BYTES", 0)
+    Checked.pending = None
+    _run_tiny("cuda", Checked, dtype=torch.bfloat16, hidden=256, heads=2, layers=1, block_size=16)
+    assert seen["split"] > 0, "no mixed step took the split route"
+    assert seen["err"] <= 2e-2, seen

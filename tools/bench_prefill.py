@@ -24,6 +24,7 @@ SHAPES = {
     "batch2k": [(2048, 2048)] * 8,
     "chunk32k": [(32768, 2048)],
     "mixed": [(2048, 512)] * 4 + [(2048, 1)] * 60,
+    "mixed_split": [(2048, 512)] * 4 + [(2048, 1)] * 60,
     "full32k": [(32768, 32768)],
 }
 
@@ -58,7 +59,20 @@ def run(name, iters, warmup):
     maxq = max(ql for _, ql in specs)
     flops = sum(4 * HQ * D * sum(range(c - ql + 1, c + 1)) for c, ql in specs)
 
+    split = name.endswith("_split")
+    if split:
+        # the adapter's route for decode-heavy mixed steps: the varlen launch skips the one-token
+        # requests (ctx 0), the decode kernel takes them
+        is_dec = torch.tensor([ql == 1 for _, ql in specs])
+        ctx_pf = torch.where(is_dec, torch.zeros_like(ctx), ctx).to(dev)
+        rows = cu[:-1][is_dec].long().to(dev)
+        bts_dec, ctx_dec = bts_d[is_dec.to(dev)].contiguous(), ctx_d[is_dec.to(dev)].contiguous()
+
     def step():
+        if split:
+            P.paged_attention_prefill_varlen(q, kv, bts_d, cu_d, ctx_pf, maxq, out=out)
+            out.index_copy_(0, rows, P.paged_attention_decode_batched(q.index_select(0, rows), kv, bts_dec, ctx_dec))
+            return
         P.paged_attention_prefill_varlen(q, kv, bts_d, cu_d, ctx_d, maxq, out=out)
 
     for _ in range(warmup):
@@ -89,5 +103,5 @@ if __name__ == "__main__":
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--shape", default=None)
     a = ap.parse_args()
-    for n in ([a.shape] if a.shape else ["full8k", "batch2k", "chunk32k", "mixed"]):
+    for n in ([a.shape] if a.shape else ["full8k", "batch2k", "chunk32k", "mixed", "mixed_split"]):
         run(n, a.iters, a.warmup)

@@ -58,6 +58,10 @@ class StepMetadata:
     cu_q_lens: Optional[torch.Tensor] = None                 # int32 [B + 1]
     ctx_lens: Optional[torch.Tensor] = None                  # int32 [B]
     max_q_len: int = 0
+    # split route of a mixed step: the same varlen launch with the decode requests masked out
+    # (context length 0 = skipped by the kernel) + one decode launch for them
+    ctx_lens_prefill_only: Optional[torch.Tensor] = None     # int32 [B]
+    decode_kv_tokens: int = 0                                # sum of the decode requests' context lengths
 
 
 def _build_metadata(scheduled, device) -> StepMetadata:
@@ -101,7 +105,18 @@ def _build_metadata(scheduled, device) -> StepMetadata:
         md.cu_q_lens = torch.tensor(cu, dtype=torch.int32).to(device)
         md.ctx_lens = torch.tensor([s + n for s, n in zip(md.start_pos, md.num_tokens)], dtype=torch.int32).to(device)
         md.max_q_len = max(md.num_tokens)
+        if dec_rows and md.prefill_chunks:
+            md.decode_kv_tokens = sum(dec_lens)
+            md.ctx_lens_prefill_only = torch.tensor([s + n if pf else 0 for s, n, pf in
+                                                     zip(md.start_pos, md.num_tokens, md.is_prefill)],
+                                                    dtype=torch.int32).to(device)
     return md
+
+
+# Mixed steps whose decode requests read at least this many KV bytes take the split route (decode
+# kernel for the decode rows, varlen launch for the prefill chunks); below it the second launch costs
+# more than it saves.
+SPLIT_DECODE_BYTES = 32 << 20
 
 
 def _rotate_half(x: torch.Tensor) -> torch.Tensor:
@@ -150,6 +165,19 @@ def _attend(attn, ops, md: StepMetadata, q, cache, t, h, d):
     # step 4: attention through the block tables
     varlen = getattr(ops, "paged_attention_prefill_varlen", None)
     if varlen is not None and ops.prefill_tensor_core_available(cache, h):
+        decode = getattr(ops, "paged_attention_decode_batched", None)
+        kv_bytes = md.decode_kv_tokens * 2 * h * d * q.element_size()
+        if md.ctx_lens_prefill_only is not None and decode is not None and kv_bytes >= SPLIT_DECODE_BYTES:
+            # a mixed step whose decode requests stream a lot of KV: a one-token query fills 1 / 32 of a
+            # 128-row tensor-core tile and streams its KV well below the HBM rate there, so the decode rows
+            # go to the HBM-bound decode kernel and the same varlen launch skips them (measured, eager
+            # launches: 4 x 512-token chunks + 60 decode tokens at 2k context 250 us in one launch, 224 us
+            # split - the split step is already bound by its four host-side launches)
+            out = torch.empty((t, h, d), dtype=q.dtype, device=q.device)
+            varlen(q, cache, md.all_block_tables, md.cu_q_lens, md.ctx_lens_prefill_only, md.max_q_len, out=out)
+            o_dec = decode(q.index_select(0, md.decode_rows), cache, md.decode_block_tables, md.decode_ctx_lens)
+            out.index_copy_(0, md.decode_rows, o_dec)
+            return attn.out_proj(out.reshape(t, h * d))
         # tensor-core shapes: the whole mixed step (prefill chunks + decode tokens) in ONE launch
         out = varlen(q, cache, md.all_block_tables, md.cu_q_lens, md.ctx_lens, md.max_q_len)
         return attn.out_proj(out.reshape(t, h * d))
