@@ -316,6 +316,10 @@ int pa_decode_set_tuning(int units_per_sm, int guided_k, int stages, int claim_l
  * SM id, CTA start, consumers' end (globaltimer ns), units processed, finisher's end,
  * first KV block landed.  pa_decode_num_workers() entries.                              */
 int pa_decode_debug_times(void* device_buffer);
+/* Same for the tcgen05 prefill kernel: 8 int64 per CTA (grid order x, y, z): SM id,
+ * globaltimer at entry / prologue done / Q stored / first S / O complete / outputs
+ * stored, KV tiles streamed.  Null switches it off.                              */
+int pa_prefill_debug_times(void* device_buffer);
 
 /* ---- per-kernel device timing (bench.py's roofline line) ---------------------
  * pa_profile_begin(n): the next n pa_decode calls record CUDA events on their

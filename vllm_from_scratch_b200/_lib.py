@@ -83,6 +83,7 @@ SIGNATURES = {
     "pa_prefill_force_path": (c_int, [c_int]),
     "pa_decode_set_tuning": (c_int, [c_int, c_int, c_int, c_int]),
     "pa_decode_debug_times": (c_int, [c_void_p]),
+    "pa_prefill_debug_times": (c_int, [c_void_p]),
     "pa_profile_begin": (c_int, [c_int32]),
     "pa_profile_end": (c_int, [c_void_p, c_void_p, c_int32]),
 }

@@ -181,6 +181,7 @@ struct PaPrefillParams {
   float scale_log2e;
   int32_t debug;          // bring-up knob, 0 = normal
   long long* trace;       // PA_PREFILL_TRACE=1: per-tile clock64 stamps of CTA (0,0,0), else null
+  long long* cta_times;   // pa_prefill_debug_times: 8 words per CTA (smid, globaltimer stamps, KV tiles), else null
 };
 bool pa_prefill_tc_supported(const PaPrefillParams& p, int dtype, int block_size);
 int pa_launch_prefill_tc(const PaPrefillParams& p, cudaStream_t stream);    // one 128-row tile per CTA
