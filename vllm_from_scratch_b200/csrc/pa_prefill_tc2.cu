@@ -89,6 +89,30 @@ __device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
   asm("add.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
   return r;
 }
+// exp2 of two values on the FMA / ALU pipes instead of the SFU: round-to-nearest split x = n + f
+// (magic-number add), 2^f by a degree-3 minimax polynomial on [-0.5, 0.5] (max relative error 7.6e-5,
+// far below the bf16 rounding P gets), 2^n by adding n to the exponent bits.  The softmax warpgroups
+// are bound by the 4-lane-per-clock SFU (one ex2 per score); sending a share of the scores through
+// this path runs both pipes side by side.
+__device__ __forceinline__ void poly_exp2x2(uint64_t x, float& p0, float& p1) {
+  float x0, x1;
+  unpack2(x, x0, x1);
+  x = pack2(fmaxf(x0, -126.f), fmaxf(x1, -126.f));           // masked scores are -inf; also keeps 2^n normal
+  const float magic = 12582912.f;                            // 1.5 * 2^23: the low mantissa bits of x + magic hold n
+  const uint64_t t = fadd2(x, pack2(magic, magic));
+  const uint64_t n = fadd2(t, pack2(-magic, -magic));
+  const uint64_t f = ffma2(n, pack2(-1.f, -1.f), x);
+  uint64_t r = ffma2(f, pack2(0.05520550534f, 0.05520550534f), pack2(0.24261397123f, 0.24261397123f));
+  r = ffma2(r, f, pack2(0.69325476885f, 0.69325476885f));
+  r = ffma2(r, f, pack2(0.99992769957f, 0.99992769957f));
+  float r0, r1, t0, t1;
+  unpack2(r, r0, r1);
+  unpack2(t, t0, t1);
+  p0 = __uint_as_float(__float_as_uint(r0) + (__float_as_uint(t0) << 23));
+  p1 = __uint_as_float(__float_as_uint(r1) + (__float_as_uint(t1) << 23));
+}
+constexpr uint32_t kPolyExpMask = 0x22u;      // score pairs with bit (c & 7) set take the polynomial path: 2 of 8 (measured: 0 -> 1025, 2/8 -> 1052, 3/8 -> 1051, 4/8 -> 1009 TFLOP/s on full8k)
+
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
   float r;
   asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
@@ -301,9 +325,16 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
         for (int hf = 0; hf < 2; ++hf) {
 #pragma unroll
           for (int c = hf * 32; c < hf * 32 + 32; ++c) {
-            float x0, x1;
-            unpack2(ffma2(pack2(__uint_as_float(v[2 * c]), __uint_as_float(v[2 * c + 1])), scale2, negm2), x0, x1);
-            const float p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+            const uint64_t x2 = ffma2(pack2(__uint_as_float(v[2 * c]), __uint_as_float(v[2 * c + 1])), scale2, negm2);
+            float p0, p1;
+            if ((kPolyExpMask >> (c & 7)) & 1u) {
+              poly_exp2x2(x2, p0, p1);
+            } else {
+              float x0, x1;
+              unpack2(x2, x0, x1);
+              p0 = fast_exp2(x0);
+              p1 = fast_exp2(x1);
+            }
             sum2[c & 1] = fadd2(sum2[c & 1], pack2(p0, p1));
             v[c] = pack_bf16(p0, p1);
           }
