@@ -339,13 +339,11 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
             v[c] = pack_bf16(p0, p1);
           }
           tmem_st32(tS + hf * 32, v + hf * 32);
-          if (hf == 1) {
-            PA_TRACE(5 * w + 3, t);
-            tmem_wait_st();                                  // also covers the O rescale above
-            tc_fence_before();
-            mbar_arrive(bar(kBarPReady + 2 * w + hf));
-            PA_TRACE(5 * w + 4, t);
-          }
+          if (hf == 1) PA_TRACE(5 * w + 3, t);
+          tmem_wait_st();                                    // also covers the O rescale above
+          tc_fence_before();
+          mbar_arrive(bar(kBarPReady + 2 * w + hf));         // keys [0, 64) / [64, 128) of P(t) are in TMEM
+          if (hf == 1) PA_TRACE(5 * w + 4, t);
         }
         float s0, s1;
         unpack2(fadd2(sum2[0], sum2[1]), s0, s1);
@@ -428,14 +426,19 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
         umma_commit(bar(kBarSFull + w));
       };
       auto pv = [&](int w, int t, bool last) {               // O_w += P_w V(t)      (P in TMEM, V in shared memory)
-        mbar_wait(bar(kBarPReady + 2 * w + 1), t & 1);
+        // the first 64 keys' P V runs while the warpgroup still exponentiates the other 64
+        mbar_wait(bar(kBarPReady + 2 * w), t & 1);
         if (tr && t < kTraceTiles) p.trace[t * kTraceSlots + 10 + 2 * w] = clock64();
         tc_fence_after();
         const uint64_t db = kDescV | (uint64_t)(((sRing + (uint32_t)((2 * t + 1) % kRing) * kItem) & 0x3FFFFu) >> 4);
         const uint32_t d = tmem + kTmemO + (uint32_t)w * 128u, a = tmem + (uint32_t)w * 128u;
         umma_bf16_ts(d, a, db, idesc_o, t > 0 ? 1u : 0u);
 #pragma unroll
-        for (int ks = 1; ks < kTileN / 16; ++ks) umma_bf16_ts(d, a + (uint32_t)ks * 8u, db + (uint64_t)(ks * (16 * 128 >> 4)), idesc_o, 1u);
+        for (int ks = 1; ks < kTileN / 32; ++ks) umma_bf16_ts(d, a + (uint32_t)ks * 8u, db + (uint64_t)(ks * (16 * 128 >> 4)), idesc_o, 1u);
+        mbar_wait(bar(kBarPReady + 2 * w + 1), t & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int ks = kTileN / 32; ks < kTileN / 16; ++ks) umma_bf16_ts(d, a + (uint32_t)ks * 8u, db + (uint64_t)(ks * (16 * 128 >> 4)), idesc_o, 1u);
         if (last) umma_commit(bar(kBarODone + w));
       };
       mbar_wait(bar(kBarQReady), 0);
