@@ -263,20 +263,38 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
         if (t == 0) stamp(4);
         PA_TRACE(5 * w + 0, t);
         tc_fence_after();
-#pragma unroll
-        for (int cc = 0; cc < kTileN / 32; ++cc) tmem_ld32(tS + cc * 32, v + cc * 32);
+        // the scores arrive in two halves: the row maximum of keys [0, 64) is taken while keys [64, 128)
+        // are still on their way from TMEM (tiles that need the causal / ragged mask wait for both first)
+        tmem_ld32(tS, v);
+        tmem_ld32(tS + 32, v + 32);
         tmem_wait_ld();
+        tmem_ld32(tS + 64, v + 64);
+        tmem_ld32(tS + 96, v + 96);
         PA_TRACE(5 * w + 1, t);
 
         const int kbase = t * kTileN;
-        if (kbase + kTileN - 1 > posw0) {                    // causal / ragged mask (warpgroup-uniform test)
+        const bool masked = kbase + kTileN - 1 > posw0;      // warpgroup-uniform
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};     // 4 independent FMNMX3 chains
+        if (!masked) {
+#pragma unroll
+          for (int c = 0; c < kTileN / 2; c += 8) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) mx4[i] = fmax3(mx4[i], __uint_as_float(v[c + 2 * i]), __uint_as_float(v[c + 2 * i + 1]));
+          }
+        }
+        tmem_wait_ld();
+        if (masked) {
 #pragma unroll
           for (int c = 0; c < kTileN; ++c)
             if (kbase + c > qpos) v[c] = 0xff800000u;        // -inf, also replaces NaN from stale keys
-        }
-        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};     // 4 independent FMNMX3 chains
 #pragma unroll
-        for (int c = 0; c < kTileN; c += 8) {
+          for (int c = 0; c < kTileN / 2; c += 8) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) mx4[i] = fmax3(mx4[i], __uint_as_float(v[c + 2 * i]), __uint_as_float(v[c + 2 * i + 1]));
+          }
+        }
+#pragma unroll
+        for (int c = kTileN / 2; c < kTileN; c += 8) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) mx4[i] = fmax3(mx4[i], __uint_as_float(v[c + 2 * i]), __uint_as_float(v[c + 2 * i + 1]));
         }
