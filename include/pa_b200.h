@@ -18,7 +18,10 @@
  *  - strides are in ELEMENTS of the cache dtype; the head_dim axis is
  *    contiguous everywhere;
  *  - thread-safety: stateless launchers (one internal mutex guards a small
- *    tensor-map cache); one process per GPU in multi-GPU use.
+ *    tensor-map cache); one process per GPU in multi-GPU use.  The process-global
+ *    test / bring-up / measurement hooks (kernel-path forcing, split-K tuning,
+ *    per-CTA timestamps, per-kernel event timing) are NOT part of this ABI: they
+ *    live in pa_b200_debug.h.
  */
 #ifndef PA_B200_H_
 #define PA_B200_H_
@@ -30,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PA_B200_ABI_VERSION 1
+#define PA_B200_ABI_VERSION 2
 
 typedef enum PaStatus {
   PA_OK = 0,
@@ -286,49 +289,21 @@ int pa_prefill(const void* q, int64_t q_stride_t, int64_t q_stride_h,
  * PA_ERR_UNSUPPORTED for shapes outside it (see pa_prefill); the caller then
  * loops pa_prefill per sequence.                                              
  * A request with ctx_lens[s] < its q_len (e.g. ctx_lens[s] = 0) is skipped and
- * its rows of `out` are left alone: callers mask requests out that way.        */
+ * its rows of `out` are left alone: callers mask requests out that way.  So is a
+ * request whose context needs more than `max_blocks` block-table entries (the
+ * row's readable length; the lengths live on the device, so the host cannot
+ * raise the reference's IndexError without a sync): the table is never read
+ * past max_blocks.                                                            */
 int pa_prefill_varlen(const void* q, int64_t q_stride_t, int64_t q_stride_h,
                       void* out, int64_t o_stride_t, int64_t o_stride_h,
                       const PaKvCache* cache,
-                      const int32_t* block_tables, int32_t bt_stride,
+                      const int32_t* block_tables, int32_t bt_stride, int32_t max_blocks,
                       const int32_t* cu_q_lens, const int32_t* ctx_lens,
                       int32_t batch, int32_t max_q_len, int32_t num_q_heads,
                       void* stream);
 /* 1 when pa_prefill / pa_prefill_varlen take the tensor-core path for this
  * cache and head count (pointer alignment is checked per call), else 0.       */
 int pa_prefill_tc_available(const PaKvCache* cache, int32_t num_q_heads);
-/* 0 = automatic (default: the two-tile ping-pong tcgen05 kernel); 1 = force the
- * decode-kernel formulation in pa_prefill even where a tensor-core kernel
- * applies; 2 = the one-tile-per-CTA tcgen05 kernel.  Returns the old value.     */
-int pa_prefill_force_path(int path);
-
-/* ---- test / tuning hook ---------------------------------------------------
- * 0 = automatic kernel choice (default); 1 = force the generic CUDA-core
- * decode kernel even for shapes the TMA kernel takes.  Returns the old value. */
-int pa_decode_force_path(int path);
-/* Split-K granularity of the fast path (guided self-scheduling): a unit handed out when
- * `remaining` blocks are left is about remaining / (guided_k * SMs) blocks (default 3), never
- * smaller than total / (units_per_sm * SMs) (1 .. 64, default 16).  stages: per-warp TMA ring
- * depth, 0 = as deep as shared memory allows.  claim_limit: a CTA claims its next unit
- * only while fewer than this many claimed KV blocks are unprocessed (default 48).        */
-int pa_decode_set_tuning(int units_per_sm, int guided_k, int stages, int claim_limit);
-/* Debug: when non-null, every fast-path CTA writes 6 int64 to device_buffer[6 * cta]:
- * SM id, CTA start, consumers' end (globaltimer ns), units processed, finisher's end,
- * first KV block landed.  pa_decode_num_workers() entries.                              */
-int pa_decode_debug_times(void* device_buffer);
-/* Same for the tcgen05 prefill kernel: 8 int64 per CTA (grid order x, y, z): SM id,
- * globaltimer at entry / prologue done / Q stored / first S / O complete / outputs
- * stored, KV tiles streamed.  Null switches it off.                              */
-int pa_prefill_debug_times(void* device_buffer);
-
-/* ---- per-kernel device timing (bench.py's roofline line) ---------------------
- * pa_profile_begin(n): the next n pa_decode calls record CUDA events on their
- * stream before the split-K kernel, between it and the reduce kernel, and after.
- * pa_profile_end: synchronises on those events, writes the per-call durations
- * (milliseconds) and returns how many calls were recorded (<0 on error).        */
-int pa_profile_begin(int32_t max_calls);
-int pa_profile_end(float* decode_ms_host, float* reduce_ms_host, int32_t capacity);
-
 #ifdef __cplusplus
 }
 #endif

@@ -14,10 +14,11 @@ from vllm_from_scratch_b200 import _lib  # noqa: E402
 from vllm_from_scratch_b200.build import build_library  # noqa: E402
 
 HEADER = os.path.join(ROOT, "include", "pa_b200.h")
+DEBUG_HEADER = os.path.join(ROOT, "include", "pa_b200_debug.h")
 
 
-def declared_functions():
-    src = open(HEADER).read()
+def declared_functions(header=HEADER):
+    src = open(header).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"^\s*(?:int|size_t|const char\*)\s+(pa_[a-z0-9_]+)\s*\(", src, flags=re.M)))
 
@@ -36,12 +37,20 @@ def test_header_declares_the_expected_entry_points():
 
 
 def test_library_exports_every_declared_symbol(lib):
-    for name in declared_functions():
-        assert hasattr(lib, name), f"{name} is declared in include/pa_b200.h but not exported"
+    for name in declared_functions() + declared_functions(DEBUG_HEADER):
+        assert hasattr(lib, name), f"{name} is declared in include/ but not exported"
 
 
 def test_ctypes_table_binds_exactly_the_declared_set():
     assert sorted(_lib.SIGNATURES) == declared_functions()
+    assert sorted(_lib.DEBUG_SIGNATURES) == declared_functions(DEBUG_HEADER)
+
+
+def test_process_global_hooks_are_not_in_the_public_abi():
+    public = declared_functions()
+    for name in ("pa_decode_force_path", "pa_prefill_force_path", "pa_decode_set_tuning", "pa_decode_debug_times",
+                 "pa_prefill_debug_times", "pa_profile_begin", "pa_profile_end"):
+        assert name not in public and name in _lib.DEBUG_SIGNATURES
 
 
 def test_struct_mirrors_have_the_c_layout():

@@ -11,6 +11,7 @@ from ctypes import (POINTER, Structure, c_char_p, c_int, c_int32, c_int64, c_siz
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpa_b200.so")
 
+ABI_VERSION = 2          # PA_B200_ABI_VERSION of include/pa_b200.h
 PA_BF16 = 0
 PA_F32 = 1
 
@@ -43,12 +44,11 @@ class PaPeerGather(Structure):
     ]
 
 
-# name -> (restype, argtypes); one entry per symbol declared in include/pa_b200.h
+# name -> (restype, argtypes); one entry per symbol declared in include/pa_b200.h (the drop-in ABI)
 SIGNATURES = {
     "pa_abi_version": (c_int, []),
     "pa_status_string": (c_char_p, [c_int]),
     "pa_decode_num_workers": (c_int, []),
-    "pa_decode_force_path": (c_int, [c_int]),
     "pa_decode_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
     "pa_decode_workspace_init": (c_int, [c_void_p, c_size_t, c_void_p]),
     "pa_decode": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
@@ -78,8 +78,14 @@ SIGNATURES = {
     "pa_prefill": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
                            c_void_p, c_int32, c_int32, c_int32, c_void_p, c_size_t, c_void_p]),
     "pa_prefill_varlen": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
-                                  c_void_p, c_int32, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p]),
+                                  c_void_p, c_int32, c_int32, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p]),
     "pa_prefill_tc_available": (c_int, [POINTER(PaKvCache), c_int32]),
+}
+
+# test / bring-up / measurement hooks declared in include/pa_b200_debug.h (process-global state;
+# not part of the drop-in ABI)
+DEBUG_SIGNATURES = {
+    "pa_decode_force_path": (c_int, [c_int]),
     "pa_prefill_force_path": (c_int, [c_int]),
     "pa_decode_set_tuning": (c_int, [c_int, c_int, c_int, c_int]),
     "pa_decode_debug_times": (c_int, [c_void_p]),
@@ -101,12 +107,13 @@ def load() -> ctypes.CDLL:
             f"{LIB_PATH} is missing: build it with `python -m vllm_from_scratch_b200.build` "
             "(nvcc, sm_100a).  There is no CPU / PyTorch fallback for the paged-attention path.")
     lib = ctypes.CDLL(LIB_PATH)
-    for name, (res, args) in SIGNATURES.items():
+    for name, (res, args) in list(SIGNATURES.items()) + list(DEBUG_SIGNATURES.items()):
         fn = getattr(lib, name)           # AttributeError if a declared symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.pa_abi_version() != 1:
-        raise RuntimeError(f"libpa_b200.so ABI version {lib.pa_abi_version()} != 1")
+    if lib.pa_abi_version() != ABI_VERSION:
+        raise RuntimeError(f"libpa_b200.so ABI version {lib.pa_abi_version()} != {ABI_VERSION}: rebuild it "
+                           "(python -m vllm_from_scratch_b200.build --force)")
     _lib = lib
     return lib
 

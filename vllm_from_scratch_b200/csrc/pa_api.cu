@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "../../include/pa_b200.h"
+#include "../../include/pa_b200_debug.h"
 #include "pa_common.cuh"
 
 namespace {
@@ -185,6 +186,7 @@ static int decode_impl(const void* q, int64_t q_stride_b, int64_t q_stride_h, vo
   p.kv_stride_block = cache->stride_block; p.kv_stride_head = cache->stride_head; p.kv_stride_slot = cache->stride_slot;
   p.bt_stride = bt_stride;
   p.batch = batch; p.num_q_heads = num_q_heads; p.num_kv_heads = Hkv; p.head_dim = D; p.block_size = BS;
+  p.num_blocks = cache->num_blocks;
   p.group = num_q_heads / Hkv;
   p.pos_head = 0;
   p.scale_log2e = (float)((1.0 / sqrt((double)D)) * 1.4426950408889634);
@@ -446,6 +448,7 @@ int fill_prefill_params(PaPrefillParams& p, const void* q, int64_t q_stride_t, i
   p.q_stride_t = q_stride_t; p.q_stride_h = q_stride_h; p.o_stride_t = o_stride_t; p.o_stride_h = o_stride_h;
   p.kv_stride_block = cache->stride_block; p.kv_stride_head = cache->stride_head; p.kv_stride_slot = cache->stride_slot;
   p.num_q_heads = num_q_heads; p.num_kv_heads = cache->num_kv_heads; p.head_dim = cache->head_dim;
+  p.num_blocks = cache->num_blocks;
   p.group = num_q_heads / cache->num_kv_heads;
   p.scale_log2e = (float)((1.0 / sqrt((double)cache->head_dim)) * 1.4426950408889634);
   return PA_OK;
@@ -466,9 +469,10 @@ extern "C" int pa_prefill_tc_available(const PaKvCache* cache, int32_t num_q_hea
 
 extern "C" int pa_prefill_varlen(const void* q, int64_t q_stride_t, int64_t q_stride_h, void* out, int64_t o_stride_t,
                                  int64_t o_stride_h, const PaKvCache* cache, const int32_t* block_tables,
-                                 int32_t bt_stride, const int32_t* cu_q_lens, const int32_t* ctx_lens, int32_t batch,
-                                 int32_t max_q_len, int32_t num_q_heads, void* stream) {
-  if (batch < 0 || max_q_len < 0 || !cache) return PA_ERR_BAD_ARG;
+                                 int32_t bt_stride, int32_t max_blocks, const int32_t* cu_q_lens,
+                                 const int32_t* ctx_lens, int32_t batch, int32_t max_q_len, int32_t num_q_heads,
+                                 void* stream) {
+  if (batch < 0 || max_q_len < 0 || max_blocks < 0 || !cache) return PA_ERR_BAD_ARG;
   if (batch == 0 || max_q_len == 0) return PA_OK;
   if (!q || !out || !cache->k || !cache->v || !block_tables || !cu_q_lens || !ctx_lens || bt_stride < 0)
     return PA_ERR_BAD_ARG;
@@ -476,7 +480,7 @@ extern "C" int pa_prefill_varlen(const void* q, int64_t q_stride_t, int64_t q_st
   PaPrefillParams p;
   int rc = fill_prefill_params(p, q, q_stride_t, q_stride_h, out, o_stride_t, o_stride_h, cache, num_q_heads);
   if (rc) return rc;
-  p.block_tables = block_tables; p.bt_stride = bt_stride;
+  p.block_tables = block_tables; p.bt_stride = bt_stride; p.max_blocks = max_blocks;
   p.cu_q_lens = cu_q_lens; p.ctx_lens = ctx_lens;
   p.batch = batch; p.max_q_len = max_q_len;
   if (!pa_prefill_tc_supported(p, cache->dtype, cache->block_size)) return PA_ERR_UNSUPPORTED;

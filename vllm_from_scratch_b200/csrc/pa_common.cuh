@@ -36,6 +36,7 @@ struct PaDecodeParams {
   int64_t kv_stride_block, kv_stride_head, kv_stride_slot;
   int32_t bt_stride;
   int32_t batch, num_q_heads, num_kv_heads, head_dim, block_size;
+  int32_t num_blocks;     // NB: extent of the block axis (TMA zero-fills block ids outside [0, NB))
   int32_t group;          // g = Hq / Hkv
   int32_t tile_q;         // q heads per head segment (partial rows per slot)
   int32_t q_tiles;        // ceil(g / tile_q); HS = Hkv * q_tiles
@@ -72,7 +73,23 @@ struct PaCursor {
   int n;      // nblk(s)
 };
 
-__device__ __forceinline__ int pa_ceil_div(int a, int b) { return (a + b - 1) / b; }
+__host__ __device__ __forceinline__ int pa_ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a PER-DEVICE attribute: one process may drive
+// several GPUs (paged_attention._DeviceOf), so "set once" is tracked per device ordinal.
+#include <atomic>
+struct PaPerDeviceFlag {
+  std::atomic<bool> set[64];
+  // returns the device ordinal if the attribute still has to be set on the current device, -2 if it
+  // is already set, -1 if the device cannot be determined (then: set it every time)
+  int need() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return -1; }
+    if (dev < 0 || dev >= 64) return -1;
+    return set[dev].load(std::memory_order_acquire) ? -2 : dev;
+  }
+  void done(int dev) { if (dev >= 0 && dev < 64) set[dev].store(true, std::memory_order_release); }
+};
 
 // CTA-wide exclusive scan of nblk(s) into s_cum[0..B]; every thread of the CTA must call.
 // scratch: >= 33 ints of shared memory.
@@ -177,6 +194,8 @@ struct PaPrefillParams {
   int32_t bt_stride;
   int32_t batch, num_tokens, ctx_len_single, max_q_len;
   int32_t num_q_heads, num_kv_heads, head_dim, group;
+  int32_t num_blocks;     // NB: extent of the block axis of the tensor maps
+  int32_t max_blocks;     // block-table entries readable per sequence (0 = unknown: trust ctx_lens)
   int32_t pos_head;       // which of tensor-map dims 3 / 4 is the head axis
   float scale_log2e;
   int32_t debug;          // bring-up knob, 0 = normal

@@ -816,7 +816,8 @@ struct MapKey {
   const void* base;
   int64_t sb, sh, ss;
   int32_t nh, hd;
-  int32_t box_halves, pad;
+  int32_t box_halves, nb;
+  int32_t dev, pad;
   bool operator==(const MapKey& o) const { return memcmp(this, &o, sizeof(MapKey)) == 0; }
 };
 struct MapEntry {
@@ -824,11 +825,22 @@ struct MapEntry {
   CUtensorMap map;
   int pos_head;
   bool used;
+  uint64_t stamp;                   // last use (LRU)
 };
-constexpr int kMapCache = 64;
-MapEntry g_maps[kMapCache];
-int g_map_next = 0;
+// Hashed, set-associative LRU cache: a 32-layer model has 64 decode maps + 64 prefill maps (K and V per
+// layer, two box shapes) and an engine loop cycles through all of them every step - a round-robin
+// cache smaller than that working set would re-encode on every launch.  1024 entries in 8-way sets.
+constexpr int kMapSets = 128, kMapWays = 8;
+MapEntry g_maps[kMapSets * kMapWays];
+uint64_t g_map_clock = 0;
 std::mutex g_map_mu;
+
+uint32_t map_hash(const MapKey& k) {
+  const uint64_t* w = reinterpret_cast<const uint64_t*>(&k);
+  uint64_t h = 0x9e3779b97f4a7c15ull;
+  for (size_t i = 0; i < sizeof(MapKey) / 8; ++i) h = (h ^ w[i]) * 0xff51afd7ed558ccdull, h ^= h >> 32;
+  return (uint32_t)h;
+}
 
 // Builds (or fetches) the 5-D tensor map of one K or V plane:
 //   dim0 = 64 head_dim columns (128 bytes, SWIZZLE_128B), dim1 = the 16 slots of a block,
@@ -845,21 +857,31 @@ int get_map(const void* base, const PaDecodeParams& p, CUtensorMap* out, int* po
   key.nh = p.num_kv_heads; key.hd = p.head_dim;
   if (box_halves <= 0) box_halves = p.head_dim / 64;
   key.box_halves = box_halves;
+  key.nb = p.num_blocks;
+  if (cudaGetDevice(&key.dev) != cudaSuccess) { cudaGetLastError(); key.dev = -1; }
+  static_assert(sizeof(MapKey) % 8 == 0, "hashed as 64-bit words");
   std::lock_guard<std::mutex> lock(g_map_mu);
-  for (int i = 0; i < kMapCache; ++i)
-    if (g_maps[i].used && g_maps[i].key == key) {
-      *out = g_maps[i].map; *pos_head = g_maps[i].pos_head;
+  MapEntry* set = g_maps + (map_hash(key) % kMapSets) * kMapWays;
+  MapEntry* victim = set;
+  for (int i = 0; i < kMapWays; ++i) {
+    if (set[i].used && set[i].key == key) {
+      set[i].stamp = ++g_map_clock;
+      *out = set[i].map; *pos_head = set[i].pos_head;
       return 0;
     }
+    if (!set[i].used) { if (victim->used) victim = set + i; }
+    else if (victim->used && set[i].stamp < victim->stamp) victim = set + i;
+  }
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) return -5;
-  // The block extent is deliberately the largest the strides allow: block ids are validated by
-  // the caller's allocator, and TMA zero-fills anything out of range instead of faulting.
+  // The block axis is bounded by the cache's own block count: a block id outside [0, NB) (a
+  // corrupted block table) is zero-filled by TMA instead of reading memory outside the cache.
+  if (p.num_blocks <= 0) return -1;
   const bool head_first = p.kv_stride_head <= p.kv_stride_block;
   const uint64_t halves = (uint64_t)p.head_dim / 64;
   cuuint64_t gdim[5] = {64, (cuuint64_t)kBS, halves, 0, 0};
   cuuint64_t gstr[4] = {(cuuint64_t)p.kv_stride_slot * 2, 128, 0, 0};
-  const cuuint64_t head_dim_sz = (cuuint64_t)p.num_kv_heads, blk_dim_sz = (cuuint64_t)1 << 31;
+  const cuuint64_t head_dim_sz = (cuuint64_t)p.num_kv_heads, blk_dim_sz = (cuuint64_t)p.num_blocks;
   if (head_first) {
     gdim[3] = head_dim_sz; gstr[2] = (cuuint64_t)p.kv_stride_head * 2;
     gdim[4] = blk_dim_sz;  gstr[3] = (cuuint64_t)p.kv_stride_block * 2;
@@ -874,9 +896,8 @@ int get_map(const void* base, const PaDecodeParams& p, CUtensorMap* out, int* po
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return -5;
-  MapEntry& e = g_maps[g_map_next];
-  g_map_next = (g_map_next + 1) % kMapCache;
-  e.key = key; e.map = m; e.pos_head = head_first ? 3 : 4; e.used = true;
+  MapEntry& e = *victim;
+  e.key = key; e.map = m; e.pos_head = head_first ? 3 : 4; e.used = true; e.stamp = ++g_map_clock;
   *out = m; *pos_head = e.pos_head;
   return 0;
 }
@@ -893,10 +914,11 @@ template <int HD>
 int launch(const PaDecodeParams& p, const CUtensorMap& mk, const CUtensorMap& mv, int num_sms, cudaStream_t stream) {
   const size_t smem = smem_layout(HD, p.group, p.num_stages, p.batch).total;
   auto kern = pa_decode_ws_kernel<HD>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PaPerDeviceFlag attr;
+  const int dev = attr.need();
+  if (dev != -2) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudget) != cudaSuccess) return -5;
-    attr_set = true;
+    attr.done(dev);
   }
   if (smem > (size_t)kSmemBudget) return -2;
   kern<<<num_sms, kThreads, smem, stream>>>(mk, mv, p);

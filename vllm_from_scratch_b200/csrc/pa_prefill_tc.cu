@@ -81,6 +81,7 @@ pa_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_cons
     q_start = 0; q_len = p.num_tokens; ctx = p.ctx_len_single;
   }
   if (q_len <= 0 || ctx < q_len) return;               // nothing to do / malformed: leave `out` alone
+  if (p.max_blocks > 0 && pa_ceil_div(ctx, kBS) > p.max_blocks) return;   // the table row is too short: never read past it
   const int q_tile = (int)gridDim.x - 1 - (int)blockIdx.x;      // long tiles first
   if (q_tile * R >= q_len) return;
   const int tok0 = q_tile * R;
@@ -334,11 +335,12 @@ constexpr size_t smem_bytes() {
 template <int HD>
 int launch(const PaPrefillParams& p, const CUtensorMap& mk, const CUtensorMap& mv, cudaStream_t stream) {
   auto kern = pa_prefill_tc_kernel<HD>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PaPerDeviceFlag attr;
+  const int dev = attr.need();
+  if (dev != -2) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes<HD>()) != cudaSuccess)
       return -5;
-    attr_set = true;
+    attr.done(dev);
   }
   const int R = kRows / p.group;
   dim3 grid((p.max_q_len + R - 1) / R, p.num_kv_heads, p.batch);
@@ -369,7 +371,7 @@ int pa_launch_prefill_tc(const PaPrefillParams& p_in, cudaStream_t stream) {
   memset(&kv, 0, sizeof(kv));
   kv.k = p.k; kv.v = p.v;
   kv.kv_stride_block = p.kv_stride_block; kv.kv_stride_head = p.kv_stride_head; kv.kv_stride_slot = p.kv_stride_slot;
-  kv.num_kv_heads = p.num_kv_heads; kv.head_dim = p.head_dim;
+  kv.num_kv_heads = p.num_kv_heads; kv.head_dim = p.head_dim; kv.num_blocks = p.num_blocks;
   CUtensorMap mk, mv;
   int ph = 3;
   int rc = pa_get_kv_tensor_map(p.k, kv, 1, &mk, &ph);

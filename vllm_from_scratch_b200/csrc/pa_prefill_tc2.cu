@@ -155,6 +155,7 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
   const int n_b = ntok_b > 0 ? (pos0 + ntok_cta - 1) / kTileN + 1 : 0;
   const int n = max(n_a, n_b);                               // KV tiles the CTA streams
   const int nblk_need = (pos0 + ntok_cta - 1) / kBS + 1;
+  if (p.max_blocks > 0 && pa_ceil_div(ctx, kBS) > p.max_blocks) return;   // the table row is too short: never read past it
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -501,11 +502,12 @@ constexpr size_t smem_bytes() {
 template <int HD>
 int launch(const PaPrefillParams& p, const CUtensorMap& mk, const CUtensorMap& mv, cudaStream_t stream) {
   auto kern = pa_prefill_tc2_kernel<HD>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PaPerDeviceFlag attr;
+  const int dev = attr.need();
+  if (dev != -2) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes<HD>()) != cudaSuccess)
       return -5;
-    attr_set = true;
+    attr.done(dev);
   }
   const int R2 = 2 * (kRows / p.group);
   dim3 grid((p.max_q_len + R2 - 1) / R2, p.num_kv_heads, p.batch);
@@ -527,7 +529,7 @@ int pa_launch_prefill_tc2(const PaPrefillParams& p_in, cudaStream_t stream) {
   memset(&kv, 0, sizeof(kv));
   kv.k = p.k; kv.v = p.v;
   kv.kv_stride_block = p.kv_stride_block; kv.kv_stride_head = p.kv_stride_head; kv.kv_stride_slot = p.kv_stride_slot;
-  kv.num_kv_heads = p.num_kv_heads; kv.head_dim = p.head_dim;
+  kv.num_kv_heads = p.num_kv_heads; kv.head_dim = p.head_dim; kv.num_blocks = p.num_blocks;
   CUtensorMap mk, mv;
   int ph = 3;
   int rc = pa_get_kv_tensor_map(p.k, kv, 1, &mk, &ph);

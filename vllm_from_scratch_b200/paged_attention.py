@@ -304,7 +304,8 @@ def paged_attention_decode_batched(query: torch.Tensor, kv_cache: KvCacheArg, bl
                                    workspace: Optional[torch.Tensor] = None, peers=None) -> torch.Tensor:
     """Batched decode: for every sequence b, ``softmax(q_b K_b^T / sqrt(D)) V_b`` over the
     ``seq_lens[b]`` tokens reached through ``block_tables[b]`` - i.e. the reference function
-    (paged_attention.py:67-101) looped over the batch, in two launches (split-K + reduce).
+    (paged_attention.py:67-101) looped over the batch: ONE launch on the bf16 fast path (the split-K
+    kernel merges its own partials), two (split-K + reduce) on the generic fp32 / odd-shape path.
 
     query ``[B, Hq, D]``; block_tables int32 ``[B, max_blocks]`` and seq_lens int32 ``[B]`` on the
     device (no host sync on the launch path); entries past ``ceil(seq_len / BS)`` are never read;
@@ -404,6 +405,9 @@ def paged_attention_prefill_chunk(query: torch.Tensor, kv_cache: KvCacheArg, blo
     if query.stride(2) != 1 and d > 1:
         query = query.contiguous()
     bt = block_table.to(torch.int32).contiguous()
+    need_blocks = (start_pos + t + desc.block_size - 1) // desc.block_size
+    if bt.numel() < need_blocks:            # what the reference's block_table[i // BS] raises (paged_attention.py:119-123)
+        raise IndexError(f"block_table has {bt.numel()} entries, positions up to {start_pos + t} need {need_blocks}")
     if out is None:
         out = torch.empty((t, hq, d), dtype=query.dtype, device=query.device)
     lib = _lib.load()
@@ -433,7 +437,10 @@ def paged_attention_prefill_varlen(query: torch.Tensor, kv_cache: KvCacheArg, bl
     attends causally to ``[0, pos]`` through ``block_tables[s]``; its K / V (history and the chunk
     itself) must already be in the cache.  ``cu_q_lens`` int32 ``[B + 1]`` and ``ctx_lens`` int32
     ``[B]`` live on the device; ``max_q_len`` is a host int >= every chunk length.  Shapes outside
-    the tensor-core path are looped per sequence through ``paged_attention_prefill_chunk``."""
+    the tensor-core path are looped per sequence through ``paged_attention_prefill_chunk``.
+    The lengths are device tensors, so a block-table row too short for its context cannot raise the
+    reference's IndexError here without a host sync: the kernel skips such a request (its rows of ``out``
+    are left alone) and never reads the table past ``block_tables.shape[1]``."""
     desc, kplane = _describe_cache(kv_cache)
     for name, ten in (("query", query), ("block_tables", block_tables), ("cu_q_lens", cu_q_lens),
                       ("ctx_lens", ctx_lens)):
@@ -462,8 +469,8 @@ def paged_attention_prefill_varlen(query: torch.Tensor, kv_cache: KvCacheArg, bl
     with _DeviceOf(query):
         rc = lib.pa_prefill_varlen(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(),
                                    out.stride(0), out.stride(1), ctypes.byref(desc), block_tables.data_ptr(),
-                                   block_tables.stride(0), cu.data_ptr(), cl.data_ptr(), b, int(max_q_len), hq,
-                                   _stream_ptr())
+                                   block_tables.stride(0), block_tables.shape[1], cu.data_ptr(), cl.data_ptr(), b,
+                                   int(max_q_len), hq, _stream_ptr())
     if rc == -2:        # PA_ERR_UNSUPPORTED: not a tensor-core shape -> per-sequence CUDA path
         cu_h = cu.tolist()
         cl_h = cl.tolist()
