@@ -67,6 +67,8 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer leg (default min(steps, 300))")
     ap.add_argument("--ramp-ms", type=float, default=300.0, help="untimed clock ramp before the warm-up steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the extra driver-visible points of the default run (c5_512x8k, generic_f32, head_sharded)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     return ap.parse_args()
 
@@ -207,6 +209,242 @@ def make_workload(torch, dev, wl, layers, seed):
     return pool, perm, lens, q, k_new, v_new, slots
 
 
+def config_block(wl, b, hq, hkv, world, layers, kv_bytes, esize, head_mode=False, peer_mode=False, gather="peer"):
+    """The `config` object of the JSON line.  The reference arm emits the SAME object for the same
+    workload (it describes the workload, not the implementation), so the two arms compare like for like."""
+    _, ctx, _, _, d, bs, _, desc = wl
+    par = f"sequence-sharded x{world}, one pool per GPU, no collective"
+    if head_mode:
+        par = (f"KV-head-sharded x{world}: {hkv} KV / {hq} Q heads per GPU, " +
+               ("output gather fused into the decode kernel (NVLink peer stores, " +
+                ("fence + arrival counters" if gather == "peer-counter" else
+                 "LL protocol: step number in every 8-byte word, no fence") + ", no collective call)"
+                if peer_mode else f"one NCCL all-gather of [B, Hq/{world}, D] per step"))
+    return {"workload": desc, "seqs_per_gpu": b, "context": ctx, "num_q_heads": hq, "num_kv_heads": hkv,
+            "head_dim": d, "block_size": bs, "kv_dtype_bytes": esize,
+            "kv_layout": "[2, L, NB, Hkv, BS, D] (reference pool)",
+            "block_tables": "seeded randperm, fully scattered", "parallelism": par,
+            "l2": f"inputs larger than L2: loop rotates over {layers} per-layer caches of "
+                  f"{kv_bytes / 2**20:.0f} MiB each",
+            "step": "one attention-layer decode call over the batch (bf16: ONE kernel - split-K decode that merges "
+                    "its own partials; fp32: split-K kernel + reduce kernel)"}
+
+
+class Timer:
+    """K steps on the current stream between two CUDA events.  `lead` untimed steps are queued right before
+    the first event WITHOUT draining the queue in between, so the timed steps start back to back behind work
+    that is already running (no idle gap between a host-side synchronize and the first launch, which at
+    --steps 20 used to cost 5 % of the region when 8 processes shared the host)."""
+
+    def __init__(self, torch, dist, world):
+        self.torch, self.dist, self.world = torch, dist, world
+        self.e0 = torch.cuda.Event(enable_timing=True)
+        self.e1 = torch.cuda.Event(enable_timing=True)
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+
+    def run(self, step, steps, lead=2, first=0):
+        torch = self.torch
+        self.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(lead):
+            step(first + i)
+        self.e0.record()
+        for i in range(steps):
+            step(first + lead + i)
+        self.e1.record()
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        self.barrier()
+        return self.e0.elapsed_time(self.e1), t0, t1
+
+    def max_over_ranks(self, values, dev):
+        if self.world == 1:
+            return list(values)
+        t = self.torch.tensor(list(values), device=dev, dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return t.tolist()
+
+
+def capture_steps(torch, fn, n):
+    """One CUDA graph per i in range(n) of fn(i) (warm first: tensor maps, function attributes)."""
+    for i in range(n):
+        fn(i)
+    torch.cuda.synchronize()
+    graphs = []
+    for i in range(n):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            fn(i)
+        graphs.append(g)
+    return graphs
+
+
+def strict_close(got, ref):
+    """bf16 bound of tests/test_decode_strict.py: |got - ref| <= 2e-3 + 2^-7 |ref| elementwise."""
+    return bool(((got.double() - ref.double()).abs() <= 2e-3 + 2.0 ** -7 * ref.double().abs()).all())
+
+
+def head_sharded_section(torch, dist, P, S, dev, world, rank, steps, timer):
+    """N > 1: the KV-head-sharded long-context workloads (BASELINE.json configs[2] and the 32k shape of
+    configs[4]) with the fused NVLink gather and with NCCL, each parity-checked once before timing, next to the
+    one-GPU time of the SAME batch measured in this run (every rank times it on its own GPU; max is reported)."""
+    out = {}
+    for name in ("c3", "c5h"):
+        wl = WORKLOADS[name]
+        b, ctx, hq, hkv, d, bs, layers, desc = wl
+        if hkv % world:
+            continue
+        pool, bts_h, lens_h, q_h, _, _, _ = make_workload(torch, dev, wl, layers, seed=4321)       # same on every rank
+        bts, lens, q = bts_h.to(dev), lens_h.to(dev), q_h.to(dev)
+        kv_full_bytes, io_full = algorithmic_bytes(b, ctx, hq, hkv, d, bs)
+        ws = P.new_decode_workspace(b, hq, hkv, d, dev)
+        out_full = torch.empty_like(q)
+        caches = [pool.layer(i) for i in range(layers)]
+        graphs = capture_steps(torch, lambda i: P.paged_attention_decode_batched(q, caches[i], bts, lens, out=out_full, workspace=ws), layers)
+        for i in range(3 * layers):
+            graphs[i % layers].replay()
+        ms1, _, _ = timer.run(lambda i: graphs[i % layers].replay(), steps)
+        ref_full = P.paged_attention_decode_batched(q, caches[0], bts, lens).clone()
+        kvh, qh = S.shard_kv_heads(hkv, world, rank), S.shard_q_heads(hq, hkv, world, rank)
+        local = pool.kv_cache[:, :, :, kvh.start:kvh.stop].contiguous()                             # [2, L, NB, Hkv / N, BS, D]
+        del pool, caches, graphs
+        torch.cuda.empty_cache()
+        lcaches = [local[:, i] for i in range(layers)]
+        hq_l, hkv_l = len(qh), len(kvh)
+        q_l = q[:, qh.start:qh.stop].contiguous()
+        ws_l = P.new_decode_workspace(b, hq_l, hkv_l, d, dev)
+        plain = P.paged_attention_decode_batched(q_l, lcaches[0], bts, lens)
+        want = torch.empty(world, b, hq_l, d, dtype=torch.bfloat16, device=dev)
+        dist.all_gather_into_tensor(want.view(-1), plain.view(-1))
+        entry = {"workload": desc, "batch": b, "context": ctx, "kv_heads_per_gpu": hkv_l, "layers_rotated": layers,
+                 "one_gpu_us_per_step": None, "arms": {}}
+        arms = {}
+        # ---- fused gather (LL): decode + receive per layer cache as CUDA graphs, buffer sets alternate ----
+        pg = S.PeerGather(b, hq, hkv, d, dev, world=world, rank=rank, protocol="ll")
+        got = pg.decode(q_l, lcaches[0], bts, lens, workspace=ws_l, parity=0)
+        pg.check()
+        ok_bits = torch.equal(got, want)
+        ok_full = strict_close(pg.full(got), ref_full)
+        pg.decode(q_l, lcaches[1], bts, lens, workspace=ws_l, parity=1)                             # keep the parity sequence 0, 1, 0, 1 ...
+        pgraphs = capture_steps(torch, lambda i: pg.decode(q_l, lcaches[i], bts, lens, workspace=ws_l, parity=i % 2), layers)
+        for i in range(3 * layers):
+            pgraphs[i % layers].replay()
+        # lead must keep the 0 / 1 alternation: `lead` = layers (even)
+        ms_p, _, _ = timer.run(lambda i: pgraphs[i % layers].replay(), steps - steps % layers, lead=layers)
+        pg.check()
+        arms["peer_ll"] = (ms_p / (steps - steps % layers), ok_bits and ok_full,
+                           "gather fused into the decode kernel: NVLink peer stores of {data, step} words, receive kernel; "
+                           "decode + receive replayed as one CUDA graph per layer cache")
+        pg.close()
+        # ---- NCCL arm: the same decode kernel writes its slice in place + one all_gather_into_tensor ----
+        hg = S.HeadGather(b, hq, d, torch.bfloat16, dev, world=world, rank=rank)
+
+        def nccl_step(i):
+            P.paged_attention_decode_batched(q_l, lcaches[i % layers], bts, lens, out=hg.local_out(), workspace=ws_l)
+            hg.all_gather()
+
+        nccl_step(0)
+        torch.cuda.synchronize()
+        ok_n = torch.equal(hg.buf, want) and strict_close(hg.full(), ref_full)
+        how = "eager launches"
+        try:
+            ngraphs = capture_steps(torch, nccl_step, layers)
+            run_n = lambda i: ngraphs[i % layers].replay()                                          # noqa: E731
+            how = "decode + all_gather replayed as one CUDA graph per layer cache"
+        except Exception:                                                                           # noqa: BLE001 - capture of the collective refused: time it eagerly
+            torch.cuda.synchronize()
+            run_n = nccl_step
+        for i in range(3 * layers):
+            run_n(i)
+        ms_n, _, _ = timer.run(run_n, steps)
+        arms["nccl"] = (ms_n / steps, ok_n, "decode kernel + one NCCL all_gather_into_tensor of [B, Hq/N, D]; " + how)
+        ms1_max, = timer.max_over_ranks([ms1 / steps], dev)
+        entry["one_gpu_us_per_step"] = ms1_max * 1e3
+        for aname, (ms, okv, what) in arms.items():
+            ms_max, bad = timer.max_over_ranks([ms, 0.0 if okv else 1.0], dev)
+            if bad:
+                raise RuntimeError(f"bench.py head-sharded {name} / {aname}: gathered outputs differ from the ranks' own bits "
+                                   "or from the full-head single-GPU decode - refusing to time a wrong result")
+            entry["arms"][aname] = {"us_per_step": ms_max * 1e3, "tokens_per_s": b / (ms_max * 1e-3),
+                                    "kv_read_gbs_per_gpu": kv_full_bytes / world / (ms_max * 1e-3) / 1e9,
+                                    "pct_of_8tbs_per_gpu": 100.0 * kv_full_bytes / world / (ms_max * 1e-3) / 1e9 / NOMINAL_HBM_GBS,
+                                    "speedup_vs_one_gpu": ms1_max / ms_max, "parity_checked": True, "what": what}
+        out[name] = entry
+        del local, lcaches
+        torch.cuda.empty_cache()
+    return out
+
+
+def c5_point(torch, P, dev, world, rank, steps, timer):
+    """BASELINE.json configs[4]: 512 seqs x 8k context over the box, sharded by sequence: 512 / N sequences per
+    GPU (N = 1: the whole batch on one GPU, 16 GiB of KV per layer) - strong scaling on the stated batch."""
+    if 512 % world:
+        return None
+    _, ctx, hq, hkv, d, bs, _, _ = WORKLOADS["c5"]
+    b = 512 // world
+    layers = 1 if b * ctx * hkv * d * 4 >= (8 << 30) else 2
+    wl = (b, ctx, hq, hkv, d, bs, layers, "")
+    pool, bts_h, lens_h, q_h, _, _, _ = make_workload(torch, dev, wl, layers, seed=777 + rank)
+    bts, lens, q = bts_h.to(dev), lens_h.to(dev), q_h.to(dev)
+    out = torch.empty_like(q)
+    ws = P.new_decode_workspace(b, hq, hkv, d, dev)
+    caches = [pool.layer(i) for i in range(layers)]
+    graphs = capture_steps(torch, lambda i: P.paged_attention_decode_batched(q, caches[i], bts, lens, out=out, workspace=ws), layers)
+    n = max(10, min(steps, 100))
+    for i in range(3):
+        graphs[i % layers].replay()
+    ms, _, _ = timer.run(lambda i: graphs[i % layers].replay(), n)
+    ms_max, = timer.max_over_ranks([ms / n], dev)
+    kv_bytes, _ = algorithmic_bytes(b, ctx, hq, hkv, d, bs)
+    del pool, caches, graphs
+    torch.cuda.empty_cache()
+    return {"workload": "C5 whole-box decode: 512 seqs x 8192 ctx, GQA 32/8, head_dim 128, bf16, sharded by sequence",
+            "seqs_total": 512, "seqs_per_gpu": b, "n_gpus": world, "scaling": "strong (total batch fixed at 512)",
+            "steps": n, "ms_per_step": ms_max, "tokens_per_s": 512 / (ms_max * 1e-3),
+            "kv_read_gbs_per_gpu": kv_bytes / (ms_max * 1e-3) / 1e9,
+            "pct_of_8tbs_per_gpu": 100.0 * kv_bytes / (ms_max * 1e-3) / 1e9 / NOMINAL_HBM_GBS,
+            "l2": f"{kv_bytes / 2**30:.0f} GiB of KV per layer cache, {layers} cache(s) rotated"}
+
+
+def generic_f32_point(torch, P, dev, steps, timer, peak):
+    """The generic kernel (fp32 KV cache = the reference's default dtype, and every odd shape) on the C2 batch:
+    KV bytes double.  Two launches per step (split-K + reduce)."""
+    b, ctx, hq, hkv, d, bs, _, _ = WORKLOADS["c2"]
+    layers = 2
+    nblk = ctx // bs
+    nb = b * nblk + 64
+    pool = P.KVCachePool(nb, bs, hkv, d, layers, dtype=torch.float32, device=dev)
+    g = torch.Generator(device=dev).manual_seed(5)
+    flat = pool.kv_cache.view(-1)
+    for lo in range(0, flat.numel(), 1 << 28):
+        n = min(1 << 28, flat.numel() - lo)
+        flat[lo:lo + n] = torch.randn(n, generator=g, device=dev, dtype=torch.float32)
+    gc = torch.Generator().manual_seed(5)
+    bts = torch.randperm(nb, generator=gc)[: b * nblk].to(torch.int32).view(b, nblk).to(dev)
+    lens = torch.full((b,), ctx, dtype=torch.int32, device=dev)
+    q = torch.randn(b, hq, d, generator=gc).to(dev)
+    out = torch.empty_like(q)
+    ws = P.new_decode_workspace(b, hq, hkv, d, dev)
+    caches = [pool.layer(i) for i in range(layers)]
+    graphs = capture_steps(torch, lambda i: P.paged_attention_decode_batched(q, caches[i], bts, lens, out=out, workspace=ws), layers)
+    n = max(20, min(steps, 200))
+    for i in range(4):
+        graphs[i % layers].replay()
+    ms, _, _ = timer.run(lambda i: graphs[i % layers].replay(), n)
+    kv_bytes, io_bytes = algorithmic_bytes(b, ctx, hq, hkv, d, bs, esize=4)
+    ach = (kv_bytes + io_bytes) / (ms / n * 1e-3) / 1e9
+    del pool, caches, graphs
+    torch.cuda.empty_cache()
+    return {"workload": "C2 batch with an fp32 KV cache (64 x 2048, 32/8 heads, head_dim 128): generic kernel",
+            "kernel": "pa_decode_generic_kernel<float> + pa_reduce_kernel<float>", "launches_per_step": 2, "steps": n,
+            "ms_per_step": ms / n, "tokens_per_s": b / (ms / n * 1e-3), "algorithmic_bytes_per_step": kv_bytes + io_bytes,
+            "achieved_gbs": ach, "peak_gbs": peak, "frac": ach / peak, "frac_of_nominal_8tbs": ach / NOMINAL_HBM_GBS}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -224,8 +462,9 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # NCCL prints its version banner on stdout when NCCL_DEBUG is set: keep stdout to the one JSON line
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=300))
     lib = _lib.load()
+    timer = Timer(torch, dist, world)
 
     head_mode = args.shard == "head" and world > 1
     wl_name = args.workload or ("c3" if head_mode else "c2")
@@ -257,36 +496,28 @@ def run_ours(args):
     caches = [pool.layer(i) for i in range(layers)]
     kv_bytes, io_bytes = algorithmic_bytes(b, ctx, hq, hkv, d, bs)
 
-    def step(i):
+    def step_eager(i):
         if peer_mode:
-            gather.decode(q, caches[i % layers], bts, lens, workspace=ws, parity=i % 2)   # decode + fused gather + wait
+            gather.decode(q, caches[i % layers], bts, lens, workspace=ws, parity=i % 2)   # decode + fused gather + receive
             return
         P.paged_attention_decode_batched(q, caches[i % layers], bts, lens, out=out, workspace=ws)
         if head_mode:
             gather.all_gather()             # the kernel wrote its slice of the gather buffer in place
 
-    step_eager = step
-    if peer_mode:
-        # decode + fused gather + arrival wait per layer cache as CUDA graphs (the wait's step number
-        # lives on the device): at 8 GPUs the kernel is shorter than the host launch path
-        if layers % 2:
-            raise SystemExit("--gather peer needs an even --layers (the two gather buffer sets alternate)")
-        for i in range(2 * layers):                        # eager first: tensor maps, workspaces; even count
-            step_eager(i)
-        torch.cuda.synchronize()
-        graphs = []
-        for i in range(layers):
-            gr = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(gr):
-                gather.decode(q, caches[i], bts, lens, workspace=ws, parity=i % 2)
-            graphs.append(gr)
-
-        def step(i):                                       # noqa: F811
-            graphs[i % layers].replay()
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
+    # The step is replayed from one CUDA graph per layer cache: the kernel (93 us at C2, 47 us head-sharded at
+    # 8 GPUs) is shorter than the Python -> ctypes launch path when 8 processes share the host.  The graph
+    # holds exactly what the eager step launches (one kernel; + the receive kernel with the fused gather).
+    if peer_mode and layers % 2:
+        raise SystemExit("--gather peer needs an even --layers (the two gather buffer sets alternate)")
+    graphed = not (head_mode and not peer_mode)          # the NCCL arm stays eager (collective outside a graph)
+    if graphed:
+        if peer_mode:
+            for i in range(2 * layers):                  # eager first, an even count: both buffer sets warm
+                step_eager(i)
+        graphs = capture_steps(torch, step_eager, layers)
+        step = lambda i: graphs[i % layers].replay()     # noqa: E731
+    else:
+        step = step_eager
 
     sampler = ClockSampler(local)
     sampler.start()
@@ -294,43 +525,41 @@ def run_ours(args):
     t_end = time.perf_counter() + args.ramp_ms * 1e-3
     i = 0
     # head mode: every rank must run the SAME number of steps (collective / arrival counts)
-    while (i < int(args.ramp_ms * 4)) if head_mode else (time.perf_counter() < t_end):
+    while (i < int(args.ramp_ms * 4) - int(args.ramp_ms * 4) % (2 * layers)) if head_mode else (time.perf_counter() < t_end):
         step(i)
         i += 1
         if i % 64 == 0:
             torch.cuda.synchronize()
-    for i in range(max(args.warmup, 3)):
+    warm = max(args.warmup, 3)
+    warm += (-warm) % (2 * layers) if peer_mode else 0   # keep the 0 / 1 buffer-set alternation aligned
+    for i in range(warm):
         step(i)
     torch.cuda.synchronize()
 
     # ---- timed region: K steps, device time, max over ranks --------------------------------
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    e0.record()
-    for i in range(args.steps):
-        step(i)
-    e1.record()
-    torch.cuda.synchronize()
-    t1 = time.perf_counter()
-    barrier()
-    ms_total = e0.elapsed_time(e1)
+    lead = 2 * layers if peer_mode else 2
+    ms_total, t0, t1 = timer.run(step, args.steps, lead=lead)
     clocks = sampler.summary(t0, t1)
+    if peer_mode and (args.steps % 2):                   # odd K: one more step realigns the buffer sets
+        step(lead + args.steps)
 
-    # ---- per-kernel durations (roofline): same steps with events around each kernel -----------
+    # ---- per-kernel durations with events around each launch (eager; cross-check of the roofline) ----
     nprof = min(args.steps, 512)
-    lib.pa_profile_begin(nprof)
-    for i in range(nprof):
-        step_eager(i)
-    import ctypes
-    dec_ms = (ctypes.c_float * nprof)()
-    red_ms = (ctypes.c_float * nprof)()
-    got = lib.pa_profile_end(dec_ms, red_ms, nprof)
-    if got <= 0:
-        raise RuntimeError(f"pa_profile_end returned {got}")
-    dec_avg = sum(dec_ms[:got]) / got
-    red_avg = sum(red_ms[:got]) / got
+    nprof -= nprof % 2 if peer_mode else 0
+    dec_avg = red_avg = None
+    got = 0
+    if nprof > 0:
+        lib.pa_profile_begin(nprof)
+        for i in range(nprof):
+            step_eager(i)
+        import ctypes
+        dec_ms = (ctypes.c_float * nprof)()
+        red_ms = (ctypes.c_float * nprof)()
+        got = lib.pa_profile_end(dec_ms, red_ms, nprof)
+        if got <= 0:
+            raise RuntimeError(f"pa_profile_end returned {got}")
+        dec_avg = sum(dec_ms[:got]) / got
+        red_avg = sum(red_ms[:got]) / got
 
     # ---- e2e: host buffers in, host buffer out, through the public Python API ----------------
     # graph.DecodeStep: the step's inputs (q, new K / V rows, their slots, block tables, sequence
@@ -383,57 +612,44 @@ def run_ours(args):
         if head_mode:
             torch.cuda.current_stream().synchronize()
 
-    for i in range(5):
+    ne2e -= ne2e % 2 if peer_mode else 0
+    for i in range(6):
         e2e_step(i)
-    barrier()
-    torch.cuda.synchronize()
-    e0.record()
-    for i in range(ne2e):
-        e2e_step(i)
-    e1.record()
-    torch.cuda.synchronize()
-    barrier()
-    ms_e2e = e0.elapsed_time(e1)
+    ms_e2e, _, _ = timer.run(e2e_step, ne2e, lead=0)
     sampler.stop_flag.set()
 
-    if world > 1:
-        t = torch.tensor([ms_total, ms_e2e, dec_avg, red_avg], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total, ms_e2e, dec_avg, red_avg = t.tolist()
+    ms_total, ms_e2e, dec_avg_m, red_avg_m = timer.max_over_ranks([ms_total, ms_e2e, dec_avg or 0.0, red_avg or 0.0], dev)
     ms_step = ms_total / args.steps
     seqs = b if head_mode else world * b                  # head mode: all ranks work on the SAME batch
     value = seqs / (ms_step * 1e-3)
     e2e_value = seqs / (ms_e2e / ne2e * 1e-3)
     kv_gbs = world * kv_bytes / (ms_step * 1e-3) / 1e9
     peak, peak_src = peak_hbm()
-    achieved = (kv_bytes + io_bytes) / (dec_avg * 1e-3) / 1e9
+    # The timed region holds ONE decode kernel per step and nothing else on the stream (graph replays back to
+    # back), so region / launches IS the kernel's average duration including its launch gap - an upper bound.
+    kernel_ms = ms_step
+    achieved = (kv_bytes + io_bytes) / (kernel_ms * 1e-3) / 1e9
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "strong" if head_mode else "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": desc, "seqs_per_gpu": b, "context": ctx, "num_q_heads": hq, "num_kv_heads": hkv,
-                   "head_dim": d, "block_size": bs, "kv_layout": "[2, L, NB, Hkv, BS, D] (reference pool)",
-                   "block_tables": "seeded randperm, fully scattered",
-                   "parallelism": (f"KV-head-sharded x{world}: {hkv} KV / {hq} Q heads per GPU, " +
-                                   ("output gather fused into the decode kernel (NVLink peer stores, " +
-                                    ("fence + arrival counters" if args.gather == "peer-counter" else
-                                     "LL protocol: step number in every 8-byte word, no fence") +
-                                    ", no collective call)" if peer_mode else
-                                    f"one NCCL all-gather of [B, Hq/{world}, D] per step") if head_mode else
-                                   f"sequence-sharded x{world}, one pool per GPU, no collective"),
-                   "l2": f"inputs larger than L2: loop rotates over {layers} per-layer caches of "
-                         f"{kv_bytes / 2**20:.0f} MiB each",
-                   "step": "one attention-layer decode call (one fused split-K + merge kernel) over the batch"},
+        "config": config_block(wl, b, hq, hkv, world, layers, kv_bytes, 2, head_mode, peer_mode, args.gather),
         "kv_read_gbs": kv_gbs, "kv_read_gbs_per_gpu": kv_gbs / world,
         "pct_of_8tbs_per_gpu": 100.0 * kv_gbs / world / NOMINAL_HBM_GBS,
         "kv_bytes_per_step_per_gpu": kv_bytes,
+        "launch_path": ("one CUDA graph per layer cache, replayed (captures exactly the eager step's launches)"
+                        if graphed else "eager launches"),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(wl_name), "peak_source": peak_src,
-                     "kernel": "pa_decode_ws_kernel<128>", "kernel_ms": dec_avg, "reduce_kernel_ms": red_avg,
+                     "kernel": "pa_decode_ws_kernel<128>", "kernel_ms": kernel_ms,
+                     "kernel_ms_source": "CUDA events over the timed region / launches (one kernel per step, max over ranks)",
+                     "kernel_ms_event_pairs": dec_avg_m if got else None,
+                     "kernel_ms_event_pairs_note": "the same kernel launched eagerly with an event pair around every launch "
+                                                   "(adds ~2 us of event overhead per launch); cross-check only",
                      "algorithmic_bytes_per_launch": kv_bytes + io_bytes,
-                     "frac_of_nominal_8tbs": achieved / NOMINAL_HBM_GBS, "launches_timed": got},
+                     "frac_of_nominal_8tbs": achieved / NOMINAL_HBM_GBS, "launches_timed": args.steps},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": ne2e, "ms_per_step": ms_e2e / ne2e,
                 "what": "graph.DecodeStep: every input of the step starts in pinned host memory; new K / V rows, "
@@ -441,11 +657,27 @@ def run_ours(args):
                         "q from and writes out to pinned host memory in place (zero-copy over PCIe; both counted in "
                         "the byte totals); copy -> reshape_and_cache -> decode is one CUDA graph and the host waits "
                         "for the result every step; the KV pool is resident state"},
-        "gpu_launches": args.steps,       # timed region: one decode launch per step (the fast path has no reduce launch)
+        "gpu_launches": args.steps * (2 if peer_mode else 1),   # timed region: one decode kernel per step (+ the receive kernel with the fused gather)
         "clocks": clocks,
     }
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(torch, pool.kv_cache[:, 0].cpu(), bts_h, lens_h, q_h, wl, args.cpu_seconds)
+    # ---- the other driver-visible points ------------------------------------------------------------------
+    want_cpu = rank == 0 and world == 1 and not args.no_cpu_baseline
+    cpu_kv = pool.kv_cache[:, 0].cpu() if want_cpu else None
+    del pool, caches, steps_e2e
+    if graphed:
+        del graphs
+    torch.cuda.empty_cache()
+    default_run = args.workload is None and not head_mode and not args.no_extras
+    if default_run:
+        xs = max(args.steps, 50)
+        line["c5_512x8k"] = c5_point(torch, P, dev, world, rank, xs, timer)
+        if world == 1:
+            line["generic_f32"] = generic_f32_point(torch, P, dev, xs, timer, peak)
+        else:
+            from vllm_from_scratch_b200 import sharding as S
+            line["head_sharded"] = head_sharded_section(torch, dist, P, S, dev, world, rank, max(args.steps, 100), timer)
+    if want_cpu:
+        line["cpu_baseline"] = cpu_baseline(torch, cpu_kv, bts_h, lens_h, q_h, wl, args.cpu_seconds)
     if rank == 0:
         emit(line)
     if world > 1:
@@ -505,10 +737,11 @@ def _ref_worker(idx):
 
 
 def run_reference(args):
-    """--impl reference: the reference's own CPU algorithm (oracle port, decode_loop) on all host
-    cores - one process per core, one sequence per process per step (sequences are independent)."""
+    """--impl reference: the reference's own CPU algorithm (oracle port decode_loop = paged_attention.py:80-101,
+    bit-identical to the reference function) on all host cores.  A step is the SAME batch as the GPU arm's
+    (all `b` sequences of the workload, sequences are independent: one per worker process, in waves of
+    `cores`); only the step COUNT is capped so that the run ends within a few minutes."""
     rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
     import multiprocessing as mp
@@ -516,37 +749,41 @@ def run_reference(args):
     import torch
     torch.set_num_threads(1)
     wl = WORKLOADS[args.workload or ("c3" if args.shard == "head" and args.gpus > 1 else "c2")]
-    b, ctx, hq, hkv, d, bs, _, desc = wl
+    b, ctx, hq, hkv, d, bs, def_layers, desc = wl
     cores = max(1, min(os.cpu_count() or 1, b, 64))
-    nseq = cores                                   # sample: one sequence per core per step
     nblk = (ctx + bs - 1) // bs
-    nb = nseq * nblk + 8
+    nb = b * nblk + 64
     g = torch.Generator().manual_seed(1234)
     kv = torch.randn(2, nb, hkv, bs, d, generator=g).to(torch.bfloat16)
-    bts = torch.randperm(nb, generator=g)[: nseq * nblk].to(torch.int32).view(nseq, nblk)
-    q = torch.randn(nseq, hq, d, generator=g).to(torch.bfloat16)
+    bts = torch.randperm(nb, generator=g)[: b * nblk].to(torch.int32).view(b, nblk)
+    q = torch.randn(b, hq, d, generator=g).to(torch.bfloat16)
     _REF_STATE.update(wl=wl, kv=kv, bts=bts, q=q)
-    # keep the whole run within a few minutes: ~0.5-1.5 s per step
-    steps = min(args.steps, 20)
-    warmup = min(max(args.warmup, 1), 2)
     ctxmp = mp.get_context("fork")
     with ctxmp.Pool(cores) as pool:
-        for _ in range(warmup):
-            pool.map(_ref_worker, range(nseq), chunksize=1)
+        t0 = time.perf_counter()
+        pool.map(_ref_worker, range(b), chunksize=1)               # warm-up step 1, also the step-time estimate
+        est = time.perf_counter() - t0
+        budget = float(os.environ.get("BENCH_REF_SECONDS", "150"))
+        steps = max(1, min(args.steps, int(budget * 0.8 / est)))
+        warmup = max(1, min(args.warmup, int(budget * 0.2 / est)))
+        for _ in range(warmup - 1):
+            pool.map(_ref_worker, range(b), chunksize=1)
         t0 = time.perf_counter()
         for _ in range(steps):
-            pool.map(_ref_worker, range(nseq), chunksize=1)
+            pool.map(_ref_worker, range(b), chunksize=1)
         dt = time.perf_counter() - t0
-    value = nseq * steps / dt
-    kv_bytes, _ = algorithmic_bytes(nseq, ctx, hq, hkv, d, bs)
-    sample = (f"each step = {nseq} of the batch's {b} sequences (ctx {ctx}), one per process on {cores} cores, "
-              f"oracle decode_loop in bf16; {steps} steps (capped from {args.steps} to bound the run)")
+    value = b * steps / dt
+    kv_bytes, _ = algorithmic_bytes(b, ctx, hq, hkv, d, bs)
+    sample = (f"each step = all {b} sequences of the batch (ctx {ctx}), one per worker process in waves of {cores} on "
+              f"{cores} host cores, oracle decode_loop in bf16; {steps} timed steps"
+              + (f" (capped from {args.steps} to bound the run)" if steps != args.steps else ""))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warmup, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": desc, "seqs_per_gpu": b, "context": ctx, "num_q_heads": hq, "num_kv_heads": hkv,
-                   "head_dim": d, "block_size": bs, "note": "CPU arm: runs on rank 0's host cores only"},
+        "config": config_block(wl, b, hq, hkv, max(args.gpus, 1), args.layers or def_layers, kv_bytes, 2),
+        "reference_note": "CPU arm: runs on rank 0's host cores only; one layer cache (nothing on a CPU is L2-resident "
+                          "at 512 MiB); `config` is the GPU arm's workload description",
         "kv_read_gbs": kv_bytes * steps / dt / 1e9,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
                          "cpu_model": cpu_model_name(), "host_cores": os.cpu_count()},

@@ -43,6 +43,8 @@ def _replay(case, device, ops):
     trace = Trace(os.path.join(GOLDEN, f"engine_{case}.npz"))
     weights = det_weights(cfg)
     assert weights_sha(weights) == trace.weights_sha, "seeded weights differ from the ones the golden run used"
+    if ops is None:
+        from vllm_from_scratch_b200 import paged_attention as ops      # the product path: CUDA kernels, no fallback
     eng = ReplayEngine(cfg, weights, trace, device, torch_dtype(cfg), ops)
     engine_adapter.install(eng, ops=ops)
     stats = {"max_err": 0.0, "rows": 0, "tok_same": 0, "tok_checked": 0, "full_rows": 0, "scale": 0.0, "steps": 0}
