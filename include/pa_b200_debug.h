@@ -32,9 +32,10 @@ int pa_decode_force_path(int path);
  * depth, 0 = as deep as shared memory allows.  claim_limit: a CTA claims its next unit
  * only while fewer than this many claimed KV blocks are unprocessed (default 48).        */
 int pa_decode_set_tuning(int units_per_sm, int guided_k, int stages, int claim_limit);
-/* Debug: when non-null, every fast-path CTA writes 6 int64 to device_buffer[6 * cta]:
- * SM id, CTA start, consumers' end (globaltimer ns), units processed, finisher's end,
- * first KV block landed.  pa_decode_num_workers() entries.                              */
+/* Debug: when non-null, every fast-path CTA writes its timeline, 12 int64 at device_buffer[12 * cta]
+ * (globaltimer ns): [0] SM id, [1] CTA start, [2] consumers' end, [3] units processed, [4] finisher's
+ * end, [5] first KV block landed, [6] plan built, [7] first unit published, [8] first TMA load issued,
+ * [9] ticket counter found exhausted, [10..11] reserved.  pa_decode_num_workers() entries.          */
 int pa_decode_debug_times(void* device_buffer);
 /* Same for the tcgen05 prefill kernel: 8 int64 per CTA (grid order x, y, z): SM id,
  * globaltimer at entry / prologue done / Q stored / first S / O complete / outputs

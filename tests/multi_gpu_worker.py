@@ -1,7 +1,7 @@
 """Worker of tests/test_multi_gpu.py: multi-rank parity of KV-head-sharded decode.
 
 Launched as  python -m torch.distributed.run --nnodes=1 --nproc-per-node W --master-addr 127.0.0.1 \
-             tests/multi_gpu_worker.py [--steps N] [--log PATH]
+             tests/multi_gpu_worker.py [--steps N] [--out PATH]
 one rank per GPU.  Every rank builds the SAME full-head batch (same seed), keeps its KV-head slice
 ``[2, NB, Hkv / W, BS, D]`` and the matching query heads, and runs the three gather implementations:
 
@@ -65,7 +65,7 @@ def strict_ok(got, ref):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--log", default="")
+    ap.add_argument("--out", default="")
     args = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -193,9 +193,9 @@ def main():
     if rank == 0:
         text = "\n".join(ln for rl in gathered for ln in rl) + f"\nmulti_gpu_worker world {world}: {'ALL OK' if int(flag) else 'FAILED'}\n"
         print(text, flush=True)
-        if args.log:
-            os.makedirs(os.path.dirname(args.log) or ".", exist_ok=True)
-            with open(args.log, "w") as f:
+        if args.out:
+            os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
+            with open(args.out, "w") as f:
                 f.write(text)
     dist.destroy_process_group()
     sys.exit(0 if int(flag) else 1)

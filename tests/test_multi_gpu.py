@@ -31,7 +31,7 @@ def test_head_sharded_gather_parity_across_ranks(world):
     log = os.path.join(ROOT, "gpurun_out", f"multi_gpu_parity_w{world}.log")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(29610 + world),
-           os.path.join(ROOT, "tests", "multi_gpu_worker.py"), "--steps", "50", "--log", log]
+           os.path.join(ROOT, "tests", "multi_gpu_worker.py"), "--steps", "50", "--out", log]
     env = dict(os.environ, NCCL_DEBUG_FILE="/dev/stderr")
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env, cwd=ROOT)
     tail = (r.stdout[-6000:] + "\n--- stderr ---\n" + r.stderr[-3000:])

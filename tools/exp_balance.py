@@ -1,7 +1,13 @@
-"""Experiment (not part of the product): units_per_sm sweep + per-CTA timing of the decode kernel.
+"""Experiment (not part of the product): split-K tuning sweep + per-CTA timeline of the decode kernel.
 
-    python tools/exp_balance.py [c2|c3|c5]
+    python tools/exp_balance.py [c2|c3|c5] [--combos ups:gk:stages:claim,...] [--out gpurun_out/timeline_c2.json]
+
+Prints, per tuning combo, the device time per launch (CUDA graph replays over the layer caches, so the host
+launch path is out of the picture) and the per-CTA timeline of one launch taken with
+pa_decode_debug_times (include/pa_b200_debug.h): plan built, first unit published, first TMA load issued,
+first KV block landed, tickets exhausted, consumers' end, finisher's end - all relative to the earliest CTA start.
 """
+import argparse
 import json
 import os
 import sys
@@ -13,8 +19,14 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench  # noqa: E402
 from vllm_from_scratch_b200 import _lib, paged_attention as P  # noqa: E402
 
-wl_name = sys.argv[1] if len(sys.argv) > 1 else "c2"
-wl = bench.WORKLOADS[wl_name]
+ap = argparse.ArgumentParser()
+ap.add_argument("workload", nargs="?", default="c2")
+ap.add_argument("--combos", default="16:3:0:48")
+ap.add_argument("--out", default="")
+ap.add_argument("--iters", type=int, default=400)
+args = ap.parse_args()
+
+wl = bench.WORKLOADS[args.workload]
 b, ctx, hq, hkv, d, bs, layers, _ = wl
 layers = min(layers, 4)
 dev = torch.device("cuda", 0)
@@ -25,59 +37,61 @@ out = torch.empty_like(q)
 ws = P.new_decode_workspace(b, hq, hkv, d, dev)
 caches = [pool.layer(i) for i in range(layers)]
 kvb, iob = bench.algorithmic_bytes(b, ctx, hq, hkv, d, bs)
+W = 12
 
 
-def run(n):
-    for i in range(n):
-        P.paged_attention_decode_batched(q, caches[i % layers], bts, lens, out=out, workspace=ws)
+def launch(i):
+    P.paged_attention_decode_batched(q, caches[i % layers], bts, lens, out=out, workspace=ws)
 
 
-def timeit(n=300):
-    run(30)
+def timeit(n):
+    graphs = bench.capture_steps(torch, launch, layers)          # the tuning knobs are baked in at capture time
+    for i in range(40):
+        graphs[i % layers].replay()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    run(n)
+    for i in range(n):
+        graphs[i % layers].replay()
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / n * 1e3
 
 
-run(500)
+def timeline():
+    nw = lib.pa_decode_num_workers()
+    dbg = torch.zeros(nw * W, dtype=torch.int64, device=dev)
+    for i in range(8):
+        launch(i)
+    torch.cuda.synchronize()
+    lib.pa_decode_debug_times(dbg.data_ptr())
+    recs = []
+    for i in range(5):
+        launch(i)
+        torch.cuda.synchronize()
+        recs.append(dbg.cpu().numpy().reshape(nw, W).copy())
+    lib.pa_decode_debug_times(None)
+    r = recs[-1]
+    t0 = r[:, 1].min()
+    rel = lambda col: (r[:, col] - t0) / 1e3                        # noqa: E731
+    pct = lambda x: [round(float(v), 2) for v in np.percentile(x, [0, 50, 100])]     # noqa: E731
+    return {"cta_start": pct(rel(1)), "plan_built": pct(rel(6)), "first_unit_published": pct(rel(7)),
+            "first_tma_issued": pct(rel(8)), "first_block_landed": pct(rel(5)), "tickets_exhausted": pct(rel(9)),
+            "consumers_end": pct(rel(2)), "finisher_end": pct(rel(4)),
+            "units_per_cta": [int(r[:, 3].min()), int(np.median(r[:, 3])), int(r[:, 3].max())]}, np.stack(recs)
+
+
 res = {}
-combos = os.environ.get("COMBOS", "24:2:0:48,16:2:0:48,20:2:0:48,28:2:0:48,24:2:0:32,24:2:0:64,24:2:0:96,24:2:0:128,"
-                                  "16:2:0:96,20:2:0:64,24:1:0:48,16:1:0:64,12:2:0:64")
-for combo in combos.split(","):
+for combo in args.combos.split(","):
     ups, gk, st, cl = (int(x) for x in combo.split(":"))
     _lib.check(lib.pa_decode_set_tuning(ups, gk, st, cl), "set_tuning")
-    us = timeit()
-    res[combo] = us
-    print(f"units_per_sm={ups:3d} guided_k={gk} stages={st} claim={cl:3d}  {us:8.2f} us  {kvb / us / 1e3:8.1f} GB/s",
-          flush=True)
+    us = timeit(args.iters)
+    tl, recs = timeline()
+    res[combo] = {"us_per_launch": us, "kv_gbs": kvb / us / 1e3, "timeline_us_min_med_max": tl}
+    print(f"units_per_sm={ups:3d} guided_k={gk} stages={st} claim={cl:3d}  {us:8.2f} us  {kvb / us / 1e3:8.1f} GB/s", flush=True)
+    for k, v in tl.items():
+        print(f"      {k:22s} {v}", flush=True)
 lib.pa_decode_set_tuning(16, 3, 0, 48)
-
-# per-CTA timestamps
-nw = lib.pa_decode_num_workers()
-dbg = torch.zeros(nw * 6, dtype=torch.int64, device=dev)
-run(20)
-torch.cuda.synchronize()
-lib.pa_decode_debug_times(dbg.data_ptr())
-recs = []
-for i in range(4):
-    run(1)
-    torch.cuda.synchronize()
-    recs.append(dbg.cpu().numpy().reshape(nw, 6).copy())
-lib.pa_decode_debug_times(None)
-r = recs[-1]
-t0 = r[:, 1].min()
-end = (r[:, 2] - t0) / 1e3
-fend = (r[:, 4] - t0) / 1e3
-first = (r[:, 5] - t0) / 1e3
-start = (r[:, 1] - t0) / 1e3
-print(f"per-CTA us: start max {start.max():.1f}; first block med {np.median(first):.1f} max {first.max():.1f}; "
-      f"consumers end min {end.min():.1f} med {np.median(end):.1f} max {end.max():.1f}; "
-      f"finisher end med {np.median(fend):.1f} max {fend.max():.1f}; "
-      f"units per CTA min {r[:, 3].min()} max {r[:, 3].max()}", flush=True)
-os.makedirs("gpurun_out", exist_ok=True)
-np.savez(f"gpurun_out/balance_{wl_name}.npz", recs=np.stack(recs))
-json.dump(res, open(f"gpurun_out/balance_{wl_name}.json", "w"))
+if args.out:
+    os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
+    json.dump({"workload": args.workload, "results": res}, open(args.out, "w"), indent=1)

@@ -59,6 +59,7 @@ constexpr int kDescBlocks = 64;     // block-table entries per descriptor (longe
 constexpr int kMaxStages = 8;       // per-warp ring depth cap
 constexpr int kMaxPartials = 32;    // split-K partials per (sequence, KV head) segment, at most
 constexpr int kHeaderInts = 16;     // counter header: [0] unit ticket, [1] exited CTAs, then one int per segment
+constexpr int kDbgWords = 12;      // int64 words per CTA of the debug timeline (pa_decode_debug_times)
 constexpr int kMaxBatch = 4096;     // seq_lens + unit prefix sums live in shared memory
 constexpr int kSmemBudget = 227 * 1024;
 constexpr uint32_t FULL = 0xffffffffu;
@@ -317,6 +318,13 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_k) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_v) : "memory");
   }
+  auto dbg_stamp = [&](int slot) {        // one thread of the calling role: globaltimer into the CTA's timeline
+    if (p.dbg) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      p.dbg[kDbgWords * (int64_t)blockIdx.x + slot] = (long long)t;
+    }
+  };
   const int hs = p.num_kv_heads;
   int* const ticket = p.counters;                            // [0] unit ticket, [1] exited CTAs
   int* const seg_cnt = p.counters + kHeaderInts;             // [segment]
@@ -331,6 +339,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     // =========================== scheduler warp ==========================================
     build_plan(p.seq_lens, p.batch, hs, p.target_units, p.guided_k * (int)gridDim.x, s_len, s_c, s_ucum, lane);
     const int NU = s_ucum[p.batch] * hs;
+    if (lane == 0) dbg_stamp(6);                                       // plan built
     // sequences with no tokens: defined result is zeros (the reference raises, paged_attention.py:93)
     for (int s = blockIdx.x; s < p.batch; s += gridDim.x)
       if (s_len[s] == 0) {
@@ -348,7 +357,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     int nx_s = 0, nx_h = 0, nx_b0 = 0, nx_n = 0, nx_nch = 0, nx_t = 0, nx_c = 0, nx_bt0 = 0, nx_bt1 = 0;
     auto setup_next = [&]() {
       nx_t = __shfl_sync(FULL, tk, 0);
-      if (nx_t >= NU) { nx_n = 0; return; }
+      if (nx_t >= NU) { nx_n = 0; if (lane == 0) dbg_stamp(9); return; }     // tickets exhausted
       if (lane == 0) tk = atomicAdd(ticket, 1);
       const PaCursor cu = pa_locate(s_ucum, p.batch, hs, nx_t);     // (s, h, chunk, chunks)
       nx_s = cu.s; nx_h = cu.h; nx_c = cu.b; nx_nch = cu.n;
@@ -399,6 +408,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
           d.last_valid = last_valid; d.nch = nch; d.slot = t; d.slot0 = t - c;
           desc[ds] = d;
           mbar_arrive(bar_dfull + ds * 8);                           // the consumers may start loading K / V
+          if (u == 0) dbg_stamp(7);                                  // first descriptor published
           if (j0 == 0) {                                             // Q rides its own barrier: needed at math time only
             mbar_expect_tx(bar_qfull + ds * 8, q_bytes);
             bulk_load(qring + ds * q_bytes, qbase + (int64_t)cs * p.q_stride_b + (int64_t)(ch * g) * p.q_stride_h,
@@ -513,7 +523,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     if (p.dbg && fw == 0 && lane == 0) {
       unsigned long long t1;
       asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
-      p.dbg[6 * (int64_t)blockIdx.x + 4] = (long long)t1;
+      p.dbg[kDbgWords * (int64_t)blockIdx.x + 4] = (long long)t1;
     }
     return;
   }
@@ -567,6 +577,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       const uint32_t dst = my_ring + p_stage * STAGE_BYTES;
       const int c3 = head3 ? ph : phys, c4 = head3 ? phys : ph;
       mbar_expect_tx(bar, STAGE_BYTES);
+      if (produced == 0 && warp == 0) dbg_stamp(8);                  // this CTA's first TMA load goes out
       tma_load_5d(dst, &tm_k, bar, c3, c4, policy);
       tma_load_5d(dst + TILE_BYTES, &tm_v, bar, c3, c4, policy);
     }
@@ -787,7 +798,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     unsigned smid;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
     asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
-    long long* d = p.dbg + 6 * (int64_t)blockIdx.x;
+    long long* d = p.dbg + kDbgWords * (int64_t)blockIdx.x;
     d[0] = smid; d[1] = (long long)dbg_t0; d[2] = (long long)t1; d[3] = units_done; d[5] = (long long)dbg_first;
   }
 }
