@@ -269,12 +269,20 @@ class Timer:
         return t.tolist()
 
 
-def capture_steps(torch, fn, n):
-    """One CUDA graph per i in range(n) of fn(i) (warm first: tensor maps, function attributes)."""
+def capture_steps(torch, fn, n, one_graph=False):
+    """One CUDA graph per i in range(n) of fn(i) (warm first: tensor maps, function attributes); with
+    ``one_graph`` a single graph holding the n launches in order - what an engine's decode step over n layers
+    looks like, and what lets consecutive launches overlap through programmatic dependent launch."""
     for i in range(n):
         fn(i)
     torch.cuda.synchronize()
     graphs = []
+    if one_graph:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for i in range(n):
+                fn(i)
+        return [g]
     for i in range(n):
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):

@@ -24,6 +24,8 @@ ap.add_argument("workload", nargs="?", default="c2")
 ap.add_argument("--combos", default="16:3:0:48")
 ap.add_argument("--out", default="")
 ap.add_argument("--iters", type=int, default=400)
+ap.add_argument("--pdl", type=int, default=1)
+ap.add_argument("--one-graph", type=int, default=1)
 args = ap.parse_args()
 
 wl = bench.WORKLOADS[args.workload]
@@ -37,7 +39,7 @@ out = torch.empty_like(q)
 ws = P.new_decode_workspace(b, hq, hkv, d, dev)
 caches = [pool.layer(i) for i in range(layers)]
 kvb, iob = bench.algorithmic_bytes(b, ctx, hq, hkv, d, bs)
-W = 12
+W = 16
 
 
 def launch(i):
@@ -45,17 +47,19 @@ def launch(i):
 
 
 def timeit(n):
-    graphs = bench.capture_steps(torch, launch, layers)          # the tuning knobs are baked in at capture time
-    for i in range(40):
-        graphs[i % layers].replay()
+    # the tuning knobs are baked in at capture time
+    graphs = bench.capture_steps(torch, launch, layers, one_graph=bool(args.one_graph))
+    per = layers if args.one_graph else 1
+    for i in range(40 // per):
+        graphs[i % len(graphs)].replay()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for i in range(n):
-        graphs[i % layers].replay()
+    for i in range(n // per):
+        graphs[i % len(graphs)].replay()
     e1.record()
     torch.cuda.synchronize()
-    return e0.elapsed_time(e1) / n * 1e3
+    return e0.elapsed_time(e1) / (n // per * per) * 1e3
 
 
 def timeline():
@@ -78,9 +82,14 @@ def timeline():
     return {"cta_start": pct(rel(1)), "plan_built": pct(rel(6)), "first_unit_published": pct(rel(7)),
             "first_tma_issued": pct(rel(8)), "first_block_landed": pct(rel(5)), "tickets_exhausted": pct(rel(9)),
             "consumers_end": pct(rel(2)), "finisher_end": pct(rel(4)),
+            # cycles -> us at 1.965 GHz: time consumer warp 0 waited for unit descriptors / for KV data / for the
+            # hand-off area to the finishers
+            "cons_wait_desc_us": pct(r[:, 13] / 1965.0), "cons_wait_data_us": pct(r[:, 14] / 1965.0),
+            "cons_wait_handoff_us": pct(r[:, 15] / 1965.0),
             "units_per_cta": [int(r[:, 3].min()), int(np.median(r[:, 3])), int(r[:, 3].max())]}, np.stack(recs)
 
 
+lib.pa_decode_set_pdl(args.pdl)
 res = {}
 for combo in args.combos.split(","):
     ups, gk, st, cl = (int(x) for x in combo.split(":"))

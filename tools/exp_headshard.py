@@ -68,13 +68,13 @@ for world in (1, 2, 4, 8):
     pg.close()
     # per-CTA timestamps of one launch
     nw = lib.pa_decode_num_workers()
-    dbg = torch.zeros(nw * 12, dtype=torch.int64, device=dev)
+    dbg = torch.zeros(nw * 16, dtype=torch.int64, device=dev)
     lib.pa_decode_debug_times(dbg.data_ptr())
     for i in range(3):
         P.paged_attention_decode_batched(q, caches[i], bts, lens, out=out, workspace=ws)
         torch.cuda.synchronize()
     lib.pa_decode_debug_times(None)
-    r = dbg.cpu().numpy().reshape(nw, 12)
+    r = dbg.cpu().numpy().reshape(nw, 16)
     t0 = r[:, 1].min()
     end, fend, first = (r[:, 2] - t0) / 1e3, (r[:, 4] - t0) / 1e3, (r[:, 5] - t0) / 1e3
     print(f"   per-CTA us: first block med {np.median(first):.1f} max {first.max():.1f}; consumers end min {end.min():.1f} "

@@ -88,6 +88,7 @@ DEBUG_SIGNATURES = {
     "pa_decode_force_path": (c_int, [c_int]),
     "pa_prefill_force_path": (c_int, [c_int]),
     "pa_decode_set_tuning": (c_int, [c_int, c_int, c_int, c_int]),
+    "pa_decode_set_pdl": (c_int, [c_int]),
     "pa_decode_debug_times": (c_int, [c_void_p]),
     "pa_prefill_debug_times": (c_int, [c_void_p]),
     "pa_profile_begin": (c_int, [c_int32]),

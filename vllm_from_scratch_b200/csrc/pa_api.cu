@@ -42,13 +42,15 @@ struct WsLayout {
 // entered and is zero again when it returns (pa_decode_workspace_init zeroes it once).
 constexpr size_t kHeaderBytes = 1 << 20;
 
-// rows = partial rows per slot, slots = partial slots.
-WsLayout ws_layout(int batch, int64_t slots, int rows, int head_dim) {
+// rows = partial rows per slot, slots = partial slots.  `flagged`: the TMA kernel's self-validating partial
+// rows - (m, l) and the head_dim values as 16-byte words {value, flag, value, flag} - in the O area alone.
+WsLayout ws_layout(int batch, int64_t slots, int rows, int head_dim, bool flagged) {
   WsLayout w;
   w.plan_off = kHeaderBytes;
   w.ml_off = w.plan_off + align_up((size_t)(batch + 3) * 4, 256);
-  w.o_off = w.ml_off + align_up((size_t)slots * rows * sizeof(float2), 256);
-  w.total = w.o_off + align_up((size_t)slots * rows * head_dim * sizeof(float), 256);
+  w.o_off = w.ml_off + align_up(flagged ? 0 : (size_t)slots * rows * sizeof(float2), 256);
+  w.total = w.o_off + align_up(flagged ? (size_t)slots * rows * (head_dim / 2 + 1) * 16
+                                       : (size_t)slots * rows * head_dim * sizeof(float), 256);
   return w;
 }
 
@@ -109,6 +111,8 @@ extern "C" int pa_decode_set_tuning(int units_per_sm, int guided_k, int stages, 
   return PA_OK;
 }
 
+extern "C" int pa_decode_set_pdl(int on) { return pa_decode_tma_set_pdl(on); }
+
 extern "C" int pa_decode_debug_times(void* device_buffer) {
   g_dbg.store(static_cast<long long*>(device_buffer));
   return PA_OK;
@@ -130,14 +134,15 @@ extern "C" size_t pa_decode_workspace_bytes(int32_t batch, int32_t num_q_heads, 
   int ctas;
   const int64_t slots_tma = tma_slots(batch, num_kv_heads, sms);
   const int64_t slots_gen = (int64_t)batch * num_kv_heads * nt + pa_decode_generic_workers(sms, &ctas);
-  const size_t a = ws_layout(batch, slots_tma, g, head_dim).total;
-  const size_t b = ws_layout(batch, slots_gen, 8, head_dim).total;
+  const size_t a = ws_layout(batch, slots_tma, g, head_dim, true).total;
+  const size_t b = ws_layout(batch, slots_gen, 8, head_dim, false).total;
   return a > b ? a : b;
 }
 
 extern "C" int pa_decode_workspace_init(void* workspace, size_t workspace_bytes, void* stream) {
   if (!workspace || workspace_bytes < kHeaderBytes) return PA_ERR_WORKSPACE;
-  return cudaMemsetAsync(workspace, 0, kHeaderBytes, static_cast<cudaStream_t>(stream)) == cudaSuccess ? PA_OK
+  // all of it: the header must be zero, and the partial area must not hold a stale word that looks flagged
+  return cudaMemsetAsync(workspace, 0, workspace_bytes, static_cast<cudaStream_t>(stream)) == cudaSuccess ? PA_OK
                                                                                                         : PA_ERR_CUDA;
 }
 
@@ -215,7 +220,7 @@ static int decode_impl(const void* q, int64_t q_stride_b, int64_t q_stride_h, vo
     slots = (int64_t)batch * Hkv * p.q_tiles + p.num_workers;
     rows = p.tile_q;
   }
-  const WsLayout w = ws_layout(batch, slots, rows, D);
+  const WsLayout w = ws_layout(batch, slots, rows, D, tma);
   if (workspace_bytes < w.total) return PA_ERR_WORKSPACE;
   uint8_t* ws = static_cast<uint8_t*>(workspace);
   p.counters = reinterpret_cast<int32_t*>(ws);

@@ -172,6 +172,7 @@ int pa_launch_decode_generic(const PaDecodeParams& p, int dtype, int ctas, cudaS
 int pa_launch_reduce(const PaDecodeParams& p, int dtype, cudaStream_t stream);
 bool pa_decode_tma_supported(const PaDecodeParams& p, int dtype);
 int pa_decode_tma_header_ints();
+int pa_decode_tma_set_pdl(int on);
 int64_t pa_decode_tma_max_units(int batch, int num_kv_heads, int target_units);
 int pa_decode_generic_workers(int num_sms, int* ctas);
 

@@ -14,33 +14,41 @@
 //    bandwidth (the time to stream equal byte counts spreads 75 % .. 100 % across SMs, stable per
 //    SM), so a static split leaves a fifth of the SM-time idle; with the ticket the fast SMs
 //    simply take more units and every SM streams until the end.
-//  * persistent grid, one CTA per SM, 8 consumer warps + a scheduler warp + 4 finisher warps:
-//      scheduler (warp 8): claims tickets one unit ahead, maps ticket -> (s, h, chunk) by binary
-//        search over the per-sequence unit prefix sums in shared memory, reads the unit's block
-//        table entries with coalesced loads and publishes them, a unit descriptor and the unit's
+//  * persistent grid, one CTA per SM, 20 warps in four roles.  Round 1 ran producer and consumer in the
+//    same warp and merged every unit with two CTA-wide barriers; per-CTA clocks (tools/exp_balance.py,
+//    profiles/r02_decode_timeline_c2_before.json) showed the consumer warps - not HBM - setting the pace
+//    at C2: of 84 us a consumer warp waited for KV data only 6 us, but spent 14 us stalled in the TMA
+//    issue path (back-pressure of a saturated memory system lands on whoever issues), 10 us in unit
+//    merges (~1 us per unit) and 24 us in the math.  So the roles are now separate:
+//      scheduler (warp 16): builds the plan, claims tickets one unit ahead, maps ticket -> (s, h, chunk)
+//        by binary search over the per-sequence unit prefix sums in shared memory, reads the unit's
+//        block-table entries with coalesced loads and publishes them, a unit descriptor and the unit's
 //        Q rows (cp.async.bulk) into a ring of 8 descriptor slots (full / empty mbarriers).
-//      consumers (warps 0-7): block j of a unit belongs to warp j % 8.  Each warp owns a private
-//        ring of R stages (one stage = K tile + V tile of one block for one KV head, [16 tokens x
-//        D] bf16 each) and is its own TMA producer: a "load cursor" walks the descriptor ring up
-//        to R blocks ahead of the "math cursor", lane 0 issues the two TMA tensor loads of a
-//        block (cp.async.bulk.tensor 5-D, 128-byte swizzle, one instruction per tile) completing
-//        on the stage's mbarrier - 8 independent issuers and R x 8 x 8 KiB in flight per SM, also
-//        while the CTA merges a unit.  Math per block on legacy tensor cores, in the TRANSPOSED
+//      producers (warps 8-15): producer c feeds consumer c.  Block j of a unit belongs to consumer
+//        j % 8; each consumer owns a private ring of R stages (one stage = K tile + V tile of one
+//        block for one KV head, [16 tokens x D] bf16 each).  The producer's one active lane walks the
+//        descriptor ring, waits for a free stage (empty mbarrier) and issues the two TMA tensor loads
+//        of the block (cp.async.bulk.tensor 5-D, 128-byte swizzle, one instruction per tile)
+//        completing on the stage's full mbarrier - 8 independent issuers, R x 8 x 8 KiB in flight per
+//        SM, and an issue stall costs nobody but the producer.
+//      consumers (warps 0-7): math only.  Per block on legacy tensor cores, in the TRANSPOSED
 //        formulation so the GQA query heads sit in the n = 8 dimension:
 //            S^T[16 tok x 8 heads] = K[16 x D] . Q^T[D x 8]          (mma.sync m16n8k16 bf16,
 //            O^T[D x 8 heads]     += V^T[D x 16 tok] . P^T[16 x 8]     fp32 accumulate)
 //        A operands by ldmatrix (K) / ldmatrix.trans (V) straight from the swizzled tiles, P^T from
 //        the S^T accumulator layout to the B layout by movmatrix, fp32 online softmax in the exp2
 //        domain with warp-shuffle reductions.  tcgen05 needs M >= 64 and is not a fit for a <= 8-row
-//        GQA group; the kernel is bound by HBM, not by the tensor pipe.
-//  * at the end of a unit the 8 consumer warps merge their (m, l, O) through shared memory; a
-//    unit that covers its whole segment is normalised and written to `out`, otherwise the merged
-//    partial goes to the workspace (coalesced, 2 KiB at g = 4) and the unit is handed to the
-//    finisher warps, which check it in at the segment's atomic counter; for the last unit of a
-//    segment to arrive they merge the segment's partials and write `out` - no second launch, and
-//    the consumers never wait for a global-memory round trip.
+//        GQA group; the kernel is bound by HBM, not by the tensor pipe.  At the end of a unit every
+//        consumer warp drops its (m, l, O) into a shared-memory hand-off area and goes straight on
+//        to the next unit - no CTA-wide barrier.
+//      finishers (warps 17-19): merge the 8 warps' states of the unit; a unit that covers its whole
+//        segment is normalised and written to `out`, otherwise the merged partial goes to the
+//        workspace (coalesced, 2 KiB at g = 4) and the unit is checked in at the segment's atomic
+//        counter; for the last unit of a segment to arrive they merge the segment's partials and write
+//        `out` - no second launch, and the consumers never wait for a global-memory round trip.
 //  * results are bit-reproducible: the block -> warp assignment and every merge order depend only
 //    on the batch shape, never on which SM took which unit.
+#include <atomic>
 #include <cuda.h>
 #include <mutex>
 #include <string.h>
@@ -50,16 +58,20 @@
 namespace {
 
 constexpr int kBS = 16;             // tokens per block on this path
-constexpr int kConsumers = 8;       // consumer warps per CTA
-constexpr int kFinWarps = 4;        // finisher warps per CTA
-constexpr int kThreads = (kConsumers + 1 + kFinWarps) * 32;   // consumers + scheduler warp + finisher warps
-constexpr int kDescRing = 8;        // unit descriptors in flight scheduler -> consumers
-constexpr int kFinRing = 8;         // finished-unit notices in flight consumers -> finisher
+constexpr int kConsumers = 8;       // consumer (math) warps per CTA: warps 0-7, two warpgroups
+constexpr int kProducers = 8;       // TMA producer warps, one per consumer: warps 8-15
+constexpr int kSchedWarp = kConsumers + kProducers;           // warp 16
+constexpr int kFinWarps = 3;        // finisher warps per CTA: warps 17-19, unit k of the CTA belongs to finisher k % 3
+                                    //   (scheduler + finishers = one warpgroup)
+constexpr int kThreads = (kConsumers + kProducers + 1 + kFinWarps) * 32;   // 640
+constexpr int kDescRing = 8;        // unit descriptors in flight scheduler -> producers / consumers
+constexpr int kNumBars = 2 * kConsumers * 8 /* kMaxStages */ + 3 * kDescRing + kFinWarps + 1;
 constexpr int kDescBlocks = 64;     // block-table entries per descriptor (longer units span several)
-constexpr int kMaxStages = 8;       // per-warp ring depth cap
+constexpr int kMaxStages = 8;       // per-warp ring depth cap (kNumBars assumes 8)
 constexpr int kMaxPartials = 32;    // split-K partials per (sequence, KV head) segment, at most
-constexpr int kHeaderInts = 16;     // counter header: [0] unit ticket, [1] exited CTAs, then one int per segment
-constexpr int kDbgWords = 12;      // int64 words per CTA of the debug timeline (pa_decode_debug_times)
+constexpr int kHeaderInts = 16;     // counter header: [0] unit ticket, [1] exited CTAs, [2] launch epoch
+constexpr int kEpochSlot = 40;      // scratch word holding this launch's partial flag
+constexpr int kDbgWords = 16;      // int64 words per CTA of the debug timeline (pa_decode_debug_times)
 constexpr int kMaxBatch = 4096;     // seq_lens + unit prefix sums live in shared memory
 constexpr int kSmemBudget = 227 * 1024;
 constexpr uint32_t FULL = 0xffffffffu;
@@ -88,8 +100,8 @@ __host__ __device__ inline SmemLayout smem_layout(int hd, int g, int r, int batc
   L.qring = o;     o += (uint32_t)kDescRing * g * hd * 2;
   L.bt = o;        o += kDescRing * kDescBlocks * 4;
   L.desc = o;      o += kDescRing * 32;
-  L.fin = o;       o += 2 * kFinRing * 16 + 16;          // notices, merge jobs, {jobs, end}
-  L.bars = o;      o += (uint32_t)(kConsumers * kMaxStages + 3 * kDescRing + 2 * kFinRing) * 8;
+  L.fin = o;       o += 32;                              // unit merge job (2 x int4)
+  L.bars = o;      o += (uint32_t)kNumBars * 8;
   L.scratch = o;   o += 48 * 4;
   L.lens = o;      o += (uint32_t)batch * 4;
   L.cs = o;        o += (uint32_t)(batch + 1) * 4;
@@ -177,6 +189,15 @@ __device__ __forceinline__ void consumer_bar() {
   asm volatile("bar.sync 1, %0;" ::"n"(kConsumers * 32) : "memory");
 }
 __device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+// A load that may be repeated until another SM's store shows up.  The __ldcv / __ldcg intrinsics are plain
+// (non-volatile) asm to the compiler: two of them on one address are "the same value", and a polling loop
+// built on them is deleted.  This one is volatile with a memory clobber, and relaxed.gpu reads at L2.
+__device__ __forceinline__ float4 ld_poll(const float4* p) {
+  float4 v;
+  asm volatile("ld.relaxed.gpu.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
 
 // Exclusive scan of a[0 .. n) in place (shared memory), a[n] = total.  Called by ONE warp (the
 // scheduler); lanes own contiguous slices.
@@ -284,37 +305,53 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   float2* merge_ml = reinterpret_cast<float2*>(smem_gen + L.merge_ml);
   int* bt_ring = reinterpret_cast<int*>(smem_gen + L.bt);
   UnitDesc* desc = reinterpret_cast<UnitDesc*>(smem_gen + L.desc);
-  int4* fin = reinterpret_cast<int4*>(smem_gen + L.fin);               // (segment, nch, slot0, -)
+  int4* mjob = reinterpret_cast<int4*>(smem_gen + L.fin);               // [0] (s, h, nch, slot)  [1] (slot0, end, -, -)
   int* scratch = reinterpret_cast<int*>(smem_gen + L.scratch);
   int* s_len = reinterpret_cast<int*>(smem_gen + L.lens);
   int* s_c = reinterpret_cast<int*>(smem_gen + L.cs);
   int* s_ucum = reinterpret_cast<int*>(smem_gen + L.ucum);
   const uint32_t qring = smem_base + L.qring;
-  const uint32_t bar_full = smem_base + L.bars;                          // [kConsumers][kMaxStages]
-  const uint32_t bar_dfull = bar_full + kConsumers * kMaxStages * 8;     // [kDescRing]
-  const uint32_t bar_dempty = bar_dfull + kDescRing * 8;                 // [kDescRing]
+  const uint32_t bar_full = smem_base + L.bars;                          // [kConsumers][kMaxStages]  TMA -> consumer
+  const uint32_t bar_empty = bar_full + kConsumers * kMaxStages * 8;     // [kConsumers][kMaxStages]  consumer -> producer
+  const uint32_t bar_dfull = bar_empty + kConsumers * kMaxStages * 8;    // [kDescRing]
+  const uint32_t bar_dempty = bar_dfull + kDescRing * 8;                 // [kDescRing]  8 consumers + 8 producers
   const uint32_t bar_qfull = bar_dempty + kDescRing * 8;                 // [kDescRing]
-  const uint32_t bar_ffull = bar_qfull + kDescRing * 8;                  // [kFinRing]
-  const uint32_t bar_fempty = bar_ffull + kFinRing * 8;                  // [kFinRing]
+  const uint32_t bar_mfull = bar_qfull + kDescRing * 8;                  // [kFinWarps] unit k's state handed to finisher k % 3 (8 warps arrive)
+  const uint32_t bar_mempty = bar_mfull + kFinWarps * 8;                 // hand-off area free again
   const uint32_t q_bytes = (uint32_t)g * HD * 2;
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
+  // Programmatic dependent launch (the host sets the stream-serialisation attribute): the NEXT kernel of the
+  // stream may become resident on an SM as soon as this CTA has left it, instead of after the whole grid has
+  // drained, and a kernel launched that way runs its own prologue - barrier init, register re-allocation,
+  // tensor-map prefetch - while its predecessor's last CTAs are still finishing.  pdl_wait() below is the
+  // point where the predecessor's memory (ticket header, seq_lens, block tables, Q, KV, out) must be final.
+  asm volatile("griddepcontrol.launch_dependents;");
+  auto pdl_wait = [] { asm volatile("griddepcontrol.wait;" ::: "memory"); };
+
   unsigned long long dbg_t0 = 0;
   if (p.dbg && threadIdx.x == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(dbg_t0));
 
-  if (threadIdx.x == 0) {
-    for (int i = 0; i < kConsumers * kMaxStages; ++i) mbar_init(bar_full + i * 8, 1);
-    for (int i = 0; i < kDescRing; ++i) {
-      mbar_init(bar_dfull + i * 8, 1);
-      mbar_init(bar_dempty + i * 8, kConsumers);
-      mbar_init(bar_qfull + i * 8, 1);
-    }
-    for (int i = 0; i < kFinRing; ++i) {
-      mbar_init(bar_ffull + i * 8, 1);
-      mbar_init(bar_fempty + i * 8, 1);
-    }
+  // Register budget per role.  The pool setmaxnreg redistributes is what the CTA was LAUNCHED with - 640
+  // threads x 96 registers = 61440 - not the SM's 64 Ki (asking for more blocks forever).  The producers'
+  // single active lane needs next to nothing; what they give back goes to the consumers (fragments of Q,
+  // the O accumulator, K / V fragment sets in flight) and to the finishers (8 partials' loads in flight per
+  // lane): 256 x 144 + 256 x 40 + 128 x 112 = 61440.
+  // Each role's code sits entirely inside the branch that executes its setmaxnreg (ptxas only grants the
+  // larger budget to code dominated by the instruction), so the one CTA-wide barrier is issued per branch.
+  auto cta_sync = [] { asm volatile("bar.sync 0, %0;" ::"n"(kThreads) : "memory"); };
+
+  // mbarrier init spread over the CTA (154 barriers by one thread cost ~1 us of every launch)
+  for (int i = threadIdx.x; i < kNumBars; i += kThreads) {
+    const uint32_t b = bar_full + i * 8;
+    uint32_t count = 1;
+    if (b >= bar_dempty && b < bar_qfull) count = kConsumers + kProducers;
+    if (b >= bar_mfull && b < bar_mempty) count = kConsumers;   // every other barrier has ONE arriving thread
+    mbar_init(b, count);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (threadIdx.x == kThreads - 1) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_k) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_v) : "memory");
   }
@@ -326,32 +363,29 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     }
   };
   const int hs = p.num_kv_heads;
-  int* const ticket = p.counters;                            // [0] unit ticket, [1] exited CTAs
-  int* const seg_cnt = p.counters + kHeaderInts;             // [segment]
-  // The first ticket is requested before the plan is built: its latency hides behind the plan.
-  int tk = 0;
-  if (warp == kConsumers && lane == 0) tk = atomicAdd(ticket, 1);
-
-  __syncthreads();                                           // mbarriers are initialised
+  int* const ticket = p.counters;                            // [0] unit ticket, [1] exited CTAs, [2] launch epoch
+  int* const seg_cnt = p.counters + kHeaderInts;             // [segment] units checked in; zero between launches
   __nv_bfloat16* obase = static_cast<__nv_bfloat16*>(p.out);
 
-  if (warp == kConsumers) {
+  if (warp >= kSchedWarp) {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+  if (warp == kSchedWarp) {
     // =========================== scheduler warp ==========================================
+    // The plan and the first unit are prepared BEFORE the CTA-wide barrier below: nothing here needs the
+    // mbarriers, and the other warps have nothing to do until the first descriptor is published anyway.
+    // The first ticket is requested before the plan is built: its latency hides behind the plan.
+    int tk = 0, epoch = 0;
+    pdl_wait();
+    if (lane == 0) {
+      tk = atomicAdd(ticket, 1);
+      // The partial flag of this launch: epoch + 1, never 0 (a fresh workspace is all zeros).  Stable while any
+      // CTA may still read it: only the LAST scheduler to finish advances it, and every scheduler reads it here.
+      epoch = *reinterpret_cast<volatile int*>(ticket + 2);
+      scratch[kEpochSlot] = epoch + 1;
+    }
     build_plan(p.seq_lens, p.batch, hs, p.target_units, p.guided_k * (int)gridDim.x, s_len, s_c, s_ucum, lane);
     const int NU = s_ucum[p.batch] * hs;
     if (lane == 0) dbg_stamp(6);                                       // plan built
-    // sequences with no tokens: defined result is zeros (the reference raises, paged_attention.py:93)
-    for (int s = blockIdx.x; s < p.batch; s += gridDim.x)
-      if (s_len[s] == 0) {
-        for (int e = lane * 2; e < p.num_q_heads * HD; e += 64) {
-          const int64_t off = (int64_t)s * p.o_stride_b + (int64_t)(e / HD) * p.o_stride_h + e % HD;
-          *reinterpret_cast<uint32_t*>(obase + off) = 0u;
-          peer_store32(p, off, 0u);
-        }
-        __syncwarp();
-        if (lane == 0) peer_signal(p, (uint32_t)hs);
-      }
-    const __nv_bfloat16* qbase = static_cast<const __nv_bfloat16*>(p.q);
     // One unit of look-ahead: `nx_*` is claimed, located and has its first 64 block-table entries
     // in flight while the current unit is being published.
     int nx_s = 0, nx_h = 0, nx_b0 = 0, nx_n = 0, nx_nch = 0, nx_t = 0, nx_c = 0, nx_bt0 = 0, nx_bt1 = 0;
@@ -368,6 +402,21 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       nx_bt0 = lane < nx_n ? __ldg(row + lane) : 0;
       nx_bt1 = lane + 32 < nx_n ? __ldg(row + lane + 32) : 0;
     };
+    setup_next();
+    cta_sync();                                                // mbarriers are initialised
+
+    // sequences with no tokens: defined result is zeros (the reference raises, paged_attention.py:93)
+    for (int s = blockIdx.x; s < p.batch; s += gridDim.x)
+      if (s_len[s] == 0) {
+        for (int e = lane * 2; e < p.num_q_heads * HD; e += 64) {
+          const int64_t off = (int64_t)s * p.o_stride_b + (int64_t)(e / HD) * p.o_stride_h + e % HD;
+          *reinterpret_cast<uint32_t*>(obase + off) = 0u;
+          peer_store32(p, off, 0u);
+        }
+        __syncwarp();
+        if (lane == 0) peer_signal(p, (uint32_t)hs);
+      }
+    const __nv_bfloat16* qbase = static_cast<const __nv_bfloat16*>(p.q);
     int u = 0;                                                       // descriptors published so far
     // Claim-ahead is bounded in BLOCKS: a unit is published (and the next ticket claimed) only when
     // fewer than `claim_limit` published blocks are still unconsumed - enough to cover the ticket and
@@ -380,7 +429,6 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       outstanding -= hist[rel % kDescRing];
       ++rel;
     };
-    setup_next();
     while (nx_n > 0) {
       const int cs = nx_s, ch = nx_h, b0 = nx_b0, n = nx_n, nch = nx_nch, t = nx_t, c = nx_c;
       int bt0 = nx_bt0, bt1 = nx_bt1;
@@ -407,7 +455,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
           d.flags = (j0 == 0 ? kFirst : 0) | (j0 + nd == n ? kLast : 0);
           d.last_valid = last_valid; d.nch = nch; d.slot = t; d.slot0 = t - c;
           desc[ds] = d;
-          mbar_arrive(bar_dfull + ds * 8);                           // the consumers may start loading K / V
+          mbar_arrive(bar_dfull + ds * 8);                           // the producers may start loading K / V
           if (u == 0) dbg_stamp(7);                                  // first descriptor published
           if (j0 == 0) {                                             // Q rides its own barrier: needed at math time only
             mbar_expect_tx(bar_qfull + ds * 8, q_bytes);
@@ -430,111 +478,205 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       if (atomicAdd(ticket + 1, 1) == (int)gridDim.x - 1) {
         ticket[0] = 0;
         ticket[1] = 0;
+        ticket[2] = (epoch + 1) & 0x3fffffff;
       }
     }
     return;
   }
 
-  if (warp > kConsumers) {
     // =========================== finisher warps ==========================================
-    // The leader (first finisher warp) checks finished units in at their segment's counter; for
-    // the last unit of a segment to arrive the four warps merge the segment's partials (one row of
-    // the GQA group per warp) and write `out`.  Every global round trip costs microseconds while
-    // the SMs saturate HBM (tens of MB are queued ahead of it), so notices are taken in batches -
-    // lane i owns notice i, ONE fence and ONE atomic round trip serve the batch - and a merge has
-    // 16 partials' loads in flight per lane.  The consumers never wait for any of this.
-    const int fw = warp - kConsumers - 1;
-    int4* const jobs = fin + kFinRing;                          // (segment, nch, slot0, -)
-    int* const ctl = reinterpret_cast<int*>(fin + 2 * kFinRing);   // [0] jobs in this batch, [1] end of stream
-    int k = 0;
-    for (;;) {
-      if (fw == 0) {
-        int4 e = make_int4(0, 0, 0, 0);
-        int m = 0, end = 0;                                     // notices in this batch
-        for (; m < kFinRing; ++m) {
-          const int f = (k + m) % kFinRing;
-          const uint32_t par = ((k + m) / kFinRing) & 1;
-          if (m == 0) mbar_wait(bar_ffull + f * 8, par);
-          else if (!mbar_test(bar_ffull + f * 8, par)) break;
-          const int4 t = fin[f];
-          if (lane == m) e = t;
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bar_fempty + f * 8);
-          if (t.y == 0) { end = 1; ++m; break; }
-        }
-        k += m;
-        int last = 0;
-        if (lane < m && e.y > 0) {
-          __threadfence();                // cumulative: the CTA's partial writes (ordered by the notice) before the count
-          last = atomicAdd(seg_cnt + e.x, 1) == e.y - 1;
-          if (last) seg_cnt[e.x] = 0;     // self-cleaning: the header stays zero between launches
-        }
-        const unsigned todo = __ballot_sync(FULL, last);
-        if (last) jobs[__popc(todo & ((1u << lane) - 1))] = e;
-        if (lane == 0) { ctl[0] = __popc(todo); ctl[1] = end; }
-        if (todo) __threadfence();        // partials were written by other SMs: read them through L2
-      }
-      asm volatile("bar.sync 2, %0;" ::"n"(kFinWarps * 32) : "memory");
-      const int njobs = ctl[0], end = ctl[1];
-      for (int j = 0; j < njobs; ++j) {
-        const int4 e = jobs[j];
-        const int seg = e.x, nch = e.y, slot0 = e.z;
-        const int cs = seg / hs, ch = seg - cs * hs;
-        for (int row = fw; row < g; row += kFinWarps) {
-          for (int dq = lane * 4; dq < HD; dq += 128) {
-            float M = -INFINITY, Ls = 0.f;
-            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int k0 = 0; k0 < nch; k0 += 16) {
-              float2 ml[16];
-              float4 v[16];
+    pdl_wait();
+    cta_sync();                                                // mbarriers are initialised
+    // Unit k of this CTA (in the order the consumers finish them) belongs to finisher warp k % 3.  The warp merges
+    // the 8 consumer warps' (m, l, O) from the hand-off area and frees the area at once - the consumers only ever
+    // wait for THIS part.  A unit that is its segment's only one is normalised and written to `out`.  Any other
+    // unit's merged state goes to the unit's partial slot as self-validating 16-byte words {value, flag, value,
+    // flag} (flag = this launch's epoch): plain stores, no fence.  The unit also checks in at its segment's
+    // counter, and the warp whose unit is the last to check in folds the segment's partials in chunk order,
+    // polling each word until its flag shows this launch, and writes `out`.  The tail of a segment is therefore
+    // [hand-off + check-in, overlapped] -> one L2 round trip per partial -> stores; no fence sits in the chain
+    // (each costs microseconds while the SMs saturate HBM) and no warp ever waits for work that has not already
+    // reached its finisher.  Everything a lane folds is private to the lane (its value pairs, and its own copy
+    // of the heads' (m, l)), so the fold needs no shared memory and no warp-level synchronisation; the result
+    // does not depend on which warp folds.
+    const int fw = warp - kSchedWarp - 1;
+    const int fli = scratch[kEpochSlot];
+    const float flf = __int_as_float(fli);
+    float4* const W = reinterpret_cast<float4*>(p.part_o);
+    constexpr int WPR = HD / 2 + 1;                             // words per partial row: (m, l) + HD / 2 value pairs
+    constexpr int FU = 8;                                       // value words per lane in flight
+    constexpr int IPH = HD / 64;                                // consecutive items of a lane that share a head
+    const int nitems = g * (HD / 2);
+    auto ready = [&](const float4& w) { return __float_as_int(w.y) == fli && __float_as_int(w.w) == fli; };
+    for (int mi = fw;; mi += kFinWarps) {
+      mbar_wait(bar_mfull + fw * 8, (mi / kFinWarps) & 1);
+      const int4 j0 = mjob[0], j1 = mjob[1];
+      const int cs = j0.x, ch = j0.y, nch = j0.z, slot = j0.w, slot0 = j1.x, end = j1.y;
+      // Check in at the segment's counter FIRST: the round trip hides behind the merge below.  No fence is
+      // needed on either side of it - the count only elects the warp that folds the segment (the last to check
+      // in); the data that warp reads validates itself word by word.
+      int arrived = 0;
+      if (!end && nch > 1 && lane == 0) arrived = atomicAdd(seg_cnt + cs * hs + ch, 1);
+      if (!end) {
+        for (int e2 = lane; e2 < nitems; e2 += 32) {
+          const int head = e2 / (HD / 2), dp = (e2 - head * (HD / 2)) * 2;
+          float M = -INFINITY;
 #pragma unroll
-              for (int kk = 0; kk < 16; ++kk) {
-                const bool live = k0 + kk < nch;
-                const int64_t r = live ? (int64_t)(slot0 + k0 + kk) * g + row : 0;
-                ml[kk] = live ? __ldcg(p.part_ml + r) : make_float2(-INFINITY, 0.f);
-                v[kk] = live ? ldcg4(p.part_o + r * HD + dq) : make_float4(0.f, 0.f, 0.f, 0.f);
-              }
+          for (int w = 0; w < kConsumers; ++w) M = fmaxf(M, merge_ml[w * 8 + head].x);
+          float Lsum = 0.f, o0 = 0.f, o1 = 0.f;
 #pragma unroll
-              for (int kk = 0; kk < 16; ++kk) {
-                const float Mn = fmaxf(M, ml[kk].x);
-                // a live partial has a finite max (every unit holds >= 1 valid token); dead entries weigh 0
-                const float a = Mn == -INFINITY ? 0.f : exp2f(M - Mn);
-                const float b = Mn == -INFINITY ? 0.f : exp2f(ml[kk].x - Mn);
-                Ls = Ls * a + ml[kk].y * b;
-                o.x = o.x * a + v[kk].x * b; o.y = o.y * a + v[kk].y * b;
-                o.z = o.z * a + v[kk].z * b; o.w = o.w * a + v[kk].w * b;
-                M = Mn;
-              }
+          for (int w = 0; w < kConsumers; ++w) {
+            const float2 ml = merge_ml[w * 8 + head];
+            if (ml.x != -INFINITY) {
+              const float wg = exp2f(ml.x - M);
+              const float2 v = *reinterpret_cast<const float2*>(merge_o + (w * g + head) * OPITCH + dp);
+              Lsum = fmaf(ml.y, wg, Lsum);
+              o0 = fmaf(v.x, wg, o0);
+              o1 = fmaf(v.y, wg, o1);
             }
-            const float inv = 1.f / Ls;
-            const int64_t off = (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + row) * p.o_stride_h + dq;
-            const uint32_t w0 = pack_bf16(o.x * inv, o.y * inv), w1 = pack_bf16(o.z * inv, o.w * inv);
-            reinterpret_cast<uint32_t*>(obase + off)[0] = w0;
-            reinterpret_cast<uint32_t*>(obase + off)[1] = w1;
+          }
+          if (nch == 1) {
+            const float inv = 1.f / Lsum;
+            const int64_t off = (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + head) * p.o_stride_h + dp;
+            const uint32_t w0 = pack_bf16(o0 * inv, o1 * inv);
+            *reinterpret_cast<uint32_t*>(obase + off) = w0;
             peer_store32(p, off, w0);
-            peer_store32(p, off + 2, w1);
+          } else {
+            float4* row = W + ((int64_t)slot * g + head) * WPR;
+            __stcg(row + 1 + (dp >> 1), make_float4(o0, flf, o1, flf));
+            if (dp == 0) __stcg(row, make_float4(M, flf, Lsum, flf));
           }
         }
       }
-      asm volatile("bar.sync 2, %0;" ::"n"(kFinWarps * 32) : "memory");     // jobs consumed: the leader may refill
-      if (fw == 0 && lane == 0 && njobs > 0) peer_signal(p, (uint32_t)njobs);   // after the barrier: all rows are stored
+      __syncwarp();                                             // hand-off area read
+      if (lane == 0) mbar_arrive(bar_mempty);                   // the consumers may drop their next unit (or end marker)
       if (end) break;
+      if (nch == 1) {
+        if (lane == 0) peer_signal(p, 1u);                      // whole segment in one unit: its rows are stored
+        continue;
+      }
+      if (__shfl_sync(FULL, arrived, 0) != nch - 1) continue;
+      // ---- last unit of the segment to check in: fold the nch partials in chunk order.  The others' stores
+      //      were issued before or within about a microsecond of this point; each word is polled until its
+      //      flag shows this launch. ----
+      if (lane == 0) seg_cnt[cs * hs + ch] = 0;                 // self-cleaning: every unit of the segment has checked in
+      for (int e0 = 0; e0 < nitems; e0 += 32 * FU) {
+        float M[FU / IPH], Ls[FU / IPH], o[FU][2];
+#pragma unroll
+        for (int h = 0; h < FU / IPH; ++h) { M[h] = -INFINITY; Ls[h] = 0.f; }
+#pragma unroll
+        for (int u = 0; u < FU; ++u) o[u][0] = o[u][1] = 0.f;
+        const int head0 = (e0 + lane) / (HD / 2);               // item u of this batch belongs to head0 + u / IPH
+        const int idx0 = (e0 + lane) - head0 * (HD / 2);        //   and is value word idx0 + 32 * (u % IPH) of its row
+        for (int k = 0; k < nch; ++k) {
+          const float4* const base = W + (int64_t)(slot0 + k) * g * WPR;
+          float4 wv[FU], wm[FU / IPH];
+#pragma unroll
+          for (int u = 0; u < FU; ++u) {
+            const int head = head0 + u / IPH;
+            const float4* src = base + (int64_t)head * WPR;
+            wv[u] = make_float4(0.f, flf, 0.f, flf);
+            if (u % IPH == 0) wm[u / IPH] = make_float4(-INFINITY, flf, 0.f, flf);
+            if (head < g) {
+              wv[u] = ld_poll(src + 1 + idx0 + 32 * (u % IPH));
+              if (u % IPH == 0) wm[u / IPH] = ld_poll(src);
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < FU; ++u) {
+            const int head = head0 + u / IPH;
+            const float4* src = base + (int64_t)head * WPR;
+            while (!ready(wv[u])) wv[u] = ld_poll(src + 1 + idx0 + 32 * (u % IPH));
+            if (u % IPH == 0)
+              while (!ready(wm[u / IPH])) wm[u / IPH] = ld_poll(src);
+          }
+#pragma unroll
+          for (int h = 0; h < FU / IPH; ++h) {
+            // every partial holds >= 1 valid token (finite maximum); a head beyond g keeps weight 0
+            const float Mn = fmaxf(M[h], wm[h].x);
+            const float a = Mn == -INFINITY ? 0.f : exp2f(M[h] - Mn);
+            const float bw = Mn == -INFINITY ? 0.f : exp2f(wm[h].x - Mn);
+            Ls[h] = Ls[h] * a + wm[h].z * bw;
+            M[h] = Mn;
+#pragma unroll
+            for (int i = 0; i < IPH; ++i) {
+              o[h * IPH + i][0] = o[h * IPH + i][0] * a + wv[h * IPH + i].x * bw;
+              o[h * IPH + i][1] = o[h * IPH + i][1] * a + wv[h * IPH + i].z * bw;
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < FU; ++u) {
+          const int head = head0 + u / IPH;
+          if (head < g) {
+            const float inv = 1.f / Ls[u / IPH];
+            const int dp = (idx0 + 32 * (u % IPH)) * 2;
+            const int64_t off = (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + head) * p.o_stride_h + dp;
+            const uint32_t w0 = pack_bf16(o[u][0] * inv, o[u][1] * inv);
+            *reinterpret_cast<uint32_t*>(obase + off) = w0;
+            peer_store32(p, off, w0);
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) peer_signal(p, 1u);                        // after the warp-wide sync: all rows are stored
     }
-    if (p.dbg && fw == 0 && lane == 0) {
-      unsigned long long t1;
-      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
-      p.dbg[kDbgWords * (int64_t)blockIdx.x + 4] = (long long)t1;
+    if (p.dbg && lane == 0) {                                   // the last of the three warps to leave
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      atomicMax(reinterpret_cast<unsigned long long*>(p.dbg) + kDbgWords * (int64_t)blockIdx.x + 4, t);
+    }
+    return;
+  }
+
+  if (warp >= kConsumers) {
+    // =========================== producer warps ==========================================
+    // Producer c feeds consumer c: block j of a descriptor belongs to consumer j % 8.  One lane walks the
+    // descriptor ring, takes the next free stage of the consumer's private ring and issues the block's two
+    // tensor loads.  Waiting here - for a descriptor, for a free stage, or in the issue path itself when
+    // the memory system pushes back - delays nobody's math.
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    pdl_wait();
+    cta_sync();                                                // mbarriers are initialised
+    if (lane != 0) return;
+    const int c = warp - kConsumers;
+    uint64_t policy;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+    const bool head3 = p.pos_head == 3;                         // which of tensor-map dims 3 / 4 is the head axis
+    const uint32_t my_ring = smem_base + L.ring + c * (R * STAGE_BYTES);
+    const uint32_t my_full = bar_full + c * (kMaxStages * 8), my_empty = bar_empty + c * (kMaxStages * 8);
+    int stage = 0, phase = 0;
+    bool first = true;
+    for (int pu = 0;; ++pu) {
+      const int ds = pu % kDescRing;
+      mbar_wait(bar_dfull + ds * 8, (pu / kDescRing) & 1);
+      const int n = desc[ds].n;
+      if (n == 0) break;
+      const int ph = desc[ds].h;
+      for (int j = c; j < n; j += kConsumers) {
+        const int phys = bt_ring[ds * kDescBlocks + j];
+        mbar_wait(my_empty + stage * 8, phase ^ 1);             // first pass over the ring: free by construction
+        const uint32_t bar = my_full + stage * 8;
+        const uint32_t dst = my_ring + stage * STAGE_BYTES;
+        const int c3 = head3 ? ph : phys, c4 = head3 ? phys : ph;
+        mbar_expect_tx(bar, STAGE_BYTES);
+        if (first && c == 0) dbg_stamp(8);                      // this CTA's first TMA load goes out
+        first = false;
+        tma_load_5d(dst, &tm_k, bar, c3, c4, policy);
+        tma_load_5d(dst + TILE_BYTES, &tm_v, bar, c3, c4, policy);
+        if (++stage == R) { stage = 0; phase ^= 1; }
+      }
+      mbar_arrive(bar_dempty + ds * 8);                         // this descriptor's block ids are no longer needed here
     }
     return;
   }
 
   // ============================= consumer warps ============================================
-  const int ctid = threadIdx.x;                               // 0 .. 255
-  uint64_t policy;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
-  const bool head3 = p.pos_head == 3;                         // which of tensor-map dims 3 / 4 is the head axis
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 144;");
+  pdl_wait();
+  cta_sync();                                                  // mbarriers are initialised
   const uint32_t my_ring = smem_base + L.ring + warp * (R * STAGE_BYTES);
-  const uint32_t my_full = bar_full + warp * (kMaxStages * 8);
+  const uint32_t my_full = bar_full + warp * (kMaxStages * 8), my_empty = bar_empty + warp * (kMaxStages * 8);
   // per-lane constant pieces of the ldmatrix addresses
   const int k_tok = (lane & 7) + ((lane >> 3) & 1) * 8;       // K: matrices 0/1 = tokens 0-7 / 8-15
   const int k_csel = lane >> 4;                               //    matrices 2/3 = next 8 dims
@@ -546,64 +688,27 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   const int hq_c = (lane & 3) * 2;                            // first of this lane's two accumulator heads
   float* my_mo = merge_o + warp * g * OPITCH;
 
-  // ---- load cursor: walks this warp's blocks (j = warp, warp + 8, ... of every descriptor) up to R
-  //      blocks ahead of the math cursor and issues their TMA loads ---------------------------------
-  int pu = 0, pj = warp;            // descriptor index, block index within it
-  int p_known = -1;                 // descriptors up to here are known to be published
-  bool p_end = false;
-  int produced = 0, consumed = 0;   // this warp's blocks: loads issued / blocks processed
-  int p_stage = 0, c_stage = 0, c_phase = 0;
-  auto try_produce = [&](bool blocking) -> bool {
-    int ds;
-    for (;;) {
-      if (p_end) return false;
-      ds = pu % kDescRing;
-      if (pu > p_known) {
-        const uint32_t par = (pu / kDescRing) & 1;
-        if (blocking) mbar_wait(bar_dfull + ds * 8, par);
-        else if (!mbar_test(bar_dfull + ds * 8, par)) return false;
-        p_known = pu;
-      }
-      const int n = desc[ds].n;
-      if (n == 0) { p_end = true; return false; }
-      if (pj < n) break;
-      ++pu;                                             // no (more) blocks of this warp in that descriptor
-      pj = warp;
-    }
-    const int phys = bt_ring[ds * kDescBlocks + pj];
-    const int ph = desc[ds].h;
-    if (lane == 0) {
-      const uint32_t bar = my_full + p_stage * 8;
-      const uint32_t dst = my_ring + p_stage * STAGE_BYTES;
-      const int c3 = head3 ? ph : phys, c4 = head3 ? phys : ph;
-      mbar_expect_tx(bar, STAGE_BYTES);
-      if (produced == 0 && warp == 0) dbg_stamp(8);                  // this CTA's first TMA load goes out
-      tma_load_5d(dst, &tm_k, bar, c3, c4, policy);
-      tma_load_5d(dst + TILE_BYTES, &tm_v, bar, c3, c4, policy);
-    }
-    pj += kConsumers;
-    ++produced;
-    if (++p_stage == R) p_stage = 0;
-    return true;
-  };
-
+  int c_stage = 0, c_phase = 0;
   uint32_t qf[KSTEPS][2];
   float acc[KSTEPS][4];
   float m_run[2], l_run[2];
-  int units_done = 0, fin_count = 0;
-  unsigned long long dbg_first = 0;       // when this CTA's first KV block had landed
+  int units_done = 0;
+  bool dbg_seen = false;
+  long long dbg_desc_wait = 0, dbg_data_wait = 0, dbg_hand_wait = 0;   // cycles warp 0 waited for units / KV data / the hand-off area
 
   for (int cu = 0;; ++cu) {
     const int ds = cu % kDescRing;
-    mbar_wait(bar_dfull + ds * 8, (cu / kDescRing) & 1);
-    if (cu > p_known) p_known = cu;
+    {
+      const long long w0 = p.dbg ? clock64() : 0;
+      mbar_wait(bar_dfull + ds * 8, (cu / kDescRing) & 1);
+      if (p.dbg && cu > 0) dbg_desc_wait += clock64() - w0;
+    }
     const int4 d0 = reinterpret_cast<const int4*>(desc + ds)[0];      // s, h, n, flags
     const int4 d1 = reinterpret_cast<const int4*>(desc + ds)[1];      // last_valid, nch, slot, slot0
     if (d0.z == 0) break;
     const int cs = d0.x, ch = d0.y, n = d0.z, flags = d0.w;
     const int last_valid = d1.x, nch = d1.y, slot = d1.z, slot0 = d1.w;
 
-    while (produced - consumed < R && try_produce(false)) {}            // get K / V moving before waiting for Q
     if (flags & kFirst) {
       mbar_wait(bar_qfull + ds * 8, (cu / kDescRing) & 1);
       // Q^T B-fragments: b0 = Q[head = lane/4][dim = ks*16 + (lane%4)*2 + {0,1}], b1 = dim + 8
@@ -625,11 +730,13 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     }
 
     for (int cj = warp; cj < n; cj += kConsumers) {
-      while (produced - consumed < R && try_produce(false)) {}
-      if (produced == consumed) try_produce(true);       // the load cursor is exactly here: cannot block
-      __syncwarp();
-      mbar_wait(my_full + c_stage * 8, c_phase);
-      if (p.dbg && threadIdx.x == 0 && dbg_first == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(dbg_first));
+      {
+        const long long w0 = p.dbg ? clock64() : 0;
+        mbar_wait(my_full + c_stage * 8, c_phase);
+        if (p.dbg && dbg_seen) dbg_data_wait += clock64() - w0;
+      }
+      if (p.dbg && threadIdx.x == 0 && !dbg_seen) dbg_stamp(5);      // this CTA's first KV block has landed
+      dbg_seen = true;
       const uint32_t kt = my_ring + c_stage * STAGE_BYTES;
       const uint32_t vt = kt + TILE_BYTES;
 
@@ -709,19 +816,16 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
         mma_bf16(acc[mt], a, pb[0], pb[1]);
       }
 
-      // stage consumed by every lane -> it may be refilled
+      // stage consumed by every lane -> the producer may refill it
       __syncwarp();
-      ++consumed;
+      if (lane == 0) mbar_arrive(my_empty + c_stage * 8);
       if (++c_stage == R) { c_stage = 0; c_phase ^= 1; }
     }
-    // keep the ring full across the merge below, then hand the descriptor slot back
-    if (pu == cu) { pu = cu + 1; pj = warp; }             // the load cursor never reads a released slot
-    while (produced - consumed < R && try_produce(false)) {}
     __syncwarp();
-    if (lane == 0) mbar_arrive(bar_dempty + ds * 8);
+    if (lane == 0) mbar_arrive(bar_dempty + ds * 8);        // descriptor slot handed back
     if (!(flags & kLast)) continue;
 
-    // ---- end of the unit: merge the 8 warps' (m, l, O) through shared memory ---------------------
+    // ---- end of the unit: drop this warp's (m, l, O) into the hand-off area; the finishers merge ---------
     float lsum[2];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
@@ -730,6 +834,11 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       l += __shfl_xor_sync(FULL, l, 8);
       l += __shfl_xor_sync(FULL, l, 16);
       lsum[j] = l;
+    }
+    {
+      const long long w0 = p.dbg ? clock64() : 0;
+      mbar_wait(bar_mempty, (units_done & 1) ^ 1);            // the previous unit's state has been merged
+      if (p.dbg) dbg_hand_wait += clock64() - w0;
     }
     if (m_run[0] != -INFINITY) {          // warp-uniform: this warp had at least one block of the unit
 #pragma unroll
@@ -743,54 +852,22 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       if (hq_c < g) merge_ml[warp * 8 + hq_c] = make_float2(m_run[0], lsum[0]);
       if (hq_c + 1 < g) merge_ml[warp * 8 + hq_c + 1] = make_float2(m_run[1], lsum[1]);
     }
-    consumer_bar();                                            // A: every warp's state is in shared memory
-
-    for (int e2 = ctid; e2 < g * (HD / 2); e2 += kConsumers * 32) {
-      const int head = e2 / (HD / 2), dp = (e2 - head * (HD / 2)) * 2;
-      float M = -INFINITY;
-#pragma unroll
-      for (int w = 0; w < kConsumers; ++w) M = fmaxf(M, merge_ml[w * 8 + head].x);
-      float Lsum = 0.f, o0 = 0.f, o1 = 0.f;
-#pragma unroll
-      for (int w = 0; w < kConsumers; ++w) {
-        const float2 ml = merge_ml[w * 8 + head];
-        if (ml.x != -INFINITY) {
-          const float wg = exp2f(ml.x - M);
-          const float2 v = *reinterpret_cast<const float2*>(merge_o + (w * g + head) * OPITCH + dp);
-          Lsum = fmaf(ml.y, wg, Lsum);
-          o0 = fmaf(v.x, wg, o0);
-          o1 = fmaf(v.y, wg, o1);
-        }
-      }
-      if (nch == 1) {
-        const float inv = 1.f / Lsum;
-        const int64_t off = (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + head) * p.o_stride_h + dp;
-        const uint32_t w0 = pack_bf16(o0 * inv, o1 * inv);
-        *reinterpret_cast<uint32_t*>(obase + off) = w0;
-        peer_store32(p, off, w0);
-      } else {
-        *reinterpret_cast<float2*>(p.part_o + ((int64_t)slot * g + head) * HD + dp) = make_float2(o0, o1);
-        if (dp == 0) p.part_ml[(int64_t)slot * g + head] = make_float2(M, Lsum);
-      }
+    if (threadIdx.x == 0) {
+      mjob[0] = make_int4(cs, ch, nch, slot);
+      mjob[1] = make_int4(slot0, 0, 0, 0);
     }
-    consumer_bar();                       // B: merge_* are free again; the partial is complete CTA-wide
-    if (nch == 1 && ctid == 0) peer_signal(p, 1u);     // whole segment in one unit: its rows are stored
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_mfull + (units_done % kFinWarps) * 8);
     ++units_done;
-
-    if (nch > 1 && ctid == 0) {
-      // hand the finished unit to the finisher warp (notice ring; blocks only if it is 8 units behind)
-      const int f = fin_count % kFinRing;
-      mbar_wait(bar_fempty + f * 8, ((fin_count / kFinRing) & 1) ^ 1);
-      fin[f] = make_int4(cs * hs + ch, nch, slot0, 0);
-      mbar_arrive(bar_ffull + f * 8);
-    }
-    if (nch > 1) ++fin_count;
   }
-  if (ctid == 0) {                        // end of stream for the finisher
-    const int f = fin_count % kFinRing;
-    mbar_wait(bar_fempty + f * 8, ((fin_count / kFinRing) & 1) ^ 1);
-    fin[f] = make_int4(0, 0, 0, 0);
-    mbar_arrive(bar_ffull + f * 8);
+  // end of stream: one marker per finisher warp, through the same hand-off protocol
+  const int units_total = units_done;
+  for (int e = 0; e < kFinWarps; ++e) {
+    mbar_wait(bar_mempty, (units_done & 1) ^ 1);
+    if (threadIdx.x == 0) mjob[1] = make_int4(0, 1, 0, 0);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_mfull + (units_done % kFinWarps) * 8);
+    ++units_done;
   }
 
   if (p.dbg && threadIdx.x == 0) {
@@ -799,7 +876,8 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
     asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
     long long* d = p.dbg + kDbgWords * (int64_t)blockIdx.x;
-    d[0] = smid; d[1] = (long long)dbg_t0; d[2] = (long long)t1; d[3] = units_done; d[5] = (long long)dbg_first;
+    d[0] = smid; d[1] = (long long)dbg_t0; d[2] = (long long)t1; d[3] = units_total;
+    d[13] = dbg_desc_wait; d[14] = dbg_data_wait; d[15] = dbg_hand_wait;
   }
 }
 
@@ -871,6 +949,7 @@ int get_map(const void* base, const PaDecodeParams& p, CUtensorMap* out, int* po
   key.nb = p.num_blocks;
   if (cudaGetDevice(&key.dev) != cudaSuccess) { cudaGetLastError(); key.dev = -1; }
   static_assert(sizeof(MapKey) % 8 == 0, "hashed as 64-bit words");
+  static_assert(kThreads * 96 == 256 * 144 + 256 * 40 + 128 * 112, "setmaxnreg budgets must add up to the launch allocation");
   std::lock_guard<std::mutex> lock(g_map_mu);
   MapEntry* set = g_maps + (map_hash(key) % kMapSets) * kMapWays;
   MapEntry* victim = set;
@@ -921,6 +1000,8 @@ int stages_for(int hd, int g, int batch) {
   return r > kMaxStages ? kMaxStages : r;
 }
 
+std::atomic<int> g_pdl{1};          // launch with programmatic stream serialisation (pa_decode_set_pdl)
+
 template <int HD>
 int launch(const PaDecodeParams& p, const CUtensorMap& mk, const CUtensorMap& mv, int num_sms, cudaStream_t stream) {
   const size_t smem = smem_layout(HD, p.group, p.num_stages, p.batch).total;
@@ -932,13 +1013,24 @@ int launch(const PaDecodeParams& p, const CUtensorMap& mk, const CUtensorMap& mv
     attr.done(dev);
   }
   if (smem > (size_t)kSmemBudget) return -2;
-  kern<<<num_sms, kThreads, smem, stream>>>(mk, mv, p);
-  return cudaGetLastError() == cudaSuccess ? 0 : -5;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(num_sms);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = g_pdl.load() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, mk, mv, p) == cudaSuccess ? 0 : -5;
 }
 
 }  // namespace
 
 int pa_decode_tma_header_ints() { return kHeaderInts; }
+
+int pa_decode_tma_set_pdl(int on) { return g_pdl.exchange(on != 0); }
 
 int pa_get_kv_tensor_map(const void* base, const PaDecodeParams& p, int box_halves, CUtensorMap* out, int* pos_head) {
   return get_map(base, p, out, pos_head, box_halves);
