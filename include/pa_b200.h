@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PA_B200_ABI_VERSION 2
+#define PA_B200_ABI_VERSION 3
 
 typedef enum PaStatus {
   PA_OK = 0,
@@ -184,6 +184,27 @@ int pa_peer_free(void* ptr);
  * block_table int32 (device), slots int64 (device).  Integer-exact.          */
 int pa_slot_mapping(const int32_t* block_table, int32_t start_pos, int32_t num_tokens,
                     int32_t block_size, int64_t* slots, void* stream);
+
+/* ---- persistent block tables (replaces the per-step
+ *      rebuild of every request's table from Python lists, mini_vllm.py:729-739,
+ *      fed by the scheduler's appends, :195-207) ---------------------------------
+ * table int32 [num_rows, table_stride] lives on the device across steps, one row
+ * per live request.  One call per engine step, two small launches:
+ *  1. apply the scheduler's delta: updates int32 [*num_updates][3] = (row, column,
+ *     block id); *num_updates is read from DEVICE memory (at most max_updates
+ *     are applied, out-of-range entries are skipped), so the call has no per-step
+ *     host argument and can sit in a CUDA graph;
+ *  2. gather the scheduled requests' rows in scheduling order:
+ *     step_table[j, 0:n) = table[row_of[j], 0:n), n = ceil(ctx_lens[j] / BS), for
+ *     j < num_gather; row_of[j] < 0 (padding) leaves row j alone.
+ * step_table int32 [num_gather, step_stride] is what pa_decode / pa_prefill_varlen
+ * take as block_tables.  Integer-exact.  max_updates == 0 / num_gather == 0 skip
+ * the respective launch.                                                        */
+int pa_block_table_step(int32_t* table, int32_t table_stride, int32_t num_rows,
+                        const int32_t* updates, const int32_t* num_updates, int32_t max_updates,
+                        const int32_t* row_of, const int32_t* ctx_lens, int32_t num_gather,
+                        int32_t block_size, int32_t* step_table, int32_t step_stride,
+                        void* stream);
 
 /* ---- KV slot write (replaces the write loops paged_attention.py:48-51 and
  *      :119-123, and the scatter mini_vllm.py:424-427) ----------------------

@@ -40,6 +40,8 @@ class OracleOps:
         k_cache, v_cache = kv_cache
         O.reshape_and_cache_bshd(k_cache, v_cache, key, value, slot_mapping)
 
+    block_table_step = staticmethod(O.block_table_step)
+
     @staticmethod
     def paged_attention_decode_batched(query, kv_cache, block_tables, seq_lens):
         k_cache, v_cache = kv_cache
@@ -305,6 +307,10 @@ class TinyModel(nn.Module):
         hd = hidden // heads
         self.register_buffer("k_cache", torch.zeros(layers, num_blocks, block_size, heads, hd))
         self.register_buffer("v_cache", torch.zeros(layers, num_blocks, block_size, heads, hd))
+
+    # the reference MiniTransformer's names for the same modules (engine_adapter.DecodeGraphs is duck-typed on them)
+    embedding = property(lambda self: self.emb)
+    lm_head = property(lambda self: self.head)
 
     def forward(self, token_ids, positions, slot_mapping, seq_lens, is_prefill):
         x = self.emb(token_ids)

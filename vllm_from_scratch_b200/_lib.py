@@ -11,7 +11,7 @@ from ctypes import (POINTER, Structure, c_char_p, c_int, c_int32, c_int64, c_siz
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpa_b200.so")
 
-ABI_VERSION = 2          # PA_B200_ABI_VERSION of include/pa_b200.h
+ABI_VERSION = 3          # PA_B200_ABI_VERSION of include/pa_b200.h
 PA_BF16 = 0
 PA_F32 = 1
 
@@ -65,6 +65,8 @@ SIGNATURES = {
     "pa_peer_close": (c_int, [c_void_p]),
     "pa_peer_free": (c_int, [c_void_p]),
     "pa_slot_mapping": (c_int, [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]),
+    "pa_block_table_step": (c_int, [c_void_p, c_int32, c_int32, c_void_p, c_void_p, c_int32, c_void_p, c_void_p,
+                                    c_int32, c_int32, c_void_p, c_int32, c_void_p]),
     "pa_reshape_and_cache": (c_int, [c_void_p, c_void_p, c_int64, c_int64, POINTER(PaKvCache), c_void_p,
                                      c_int32, c_void_p]),
     "pa_rope_and_cache": (c_int, [c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int64, c_int32, c_void_p,

@@ -133,6 +133,39 @@ __global__ void pa_slot_mapping_kernel(const int32_t* __restrict__ bt, int32_t s
   slots[i] = (int64_t)__ldg(bt + pos / bs) * bs + pos % bs;
 }
 
+// ---- persistent block tables -----------------------------------------
+// The reference rebuilds every request's block table from Python lists each step
+// (05_mini_vllm/mini_vllm.py:729-739 builds the step's tensors, :195-207 appends block ids).  Here the
+// tables live on the device across steps ([rows, stride] int32, one row per live request); a step
+// ships only the scheduler's delta - (row, column, block id) triples - and then gathers the rows of
+// the requests it scheduled, in scheduling order, into the dense [batch, stride] table the attention
+// kernels read.  The update count is read from DEVICE memory so both launches can sit in a CUDA graph.
+__global__ void pa_table_update_kernel(int32_t* __restrict__ table, int32_t stride, int32_t rows,
+                                       const int32_t* __restrict__ updates, const int32_t* __restrict__ num_updates,
+                                       int32_t max_updates) {
+  const int n = min(max(__ldg(num_updates), 0), max_updates);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int r = __ldg(updates + 3 * i), c = __ldg(updates + 3 * i + 1), v = __ldg(updates + 3 * i + 2);
+    if ((unsigned)r < (unsigned)rows && (unsigned)c < (unsigned)stride) table[(int64_t)r * stride + c] = v;
+  }
+}
+
+// grid.x = gathered row j: step_table[j, 0 : n) = table[row_of[j], 0 : n), n = ceil(ctx_lens[j] / BS)
+// entries (all a kernel may dereference for that request); row_of[j] < 0 (padding) leaves the row alone.
+__global__ void __launch_bounds__(128)
+pa_table_gather_kernel(const int32_t* __restrict__ table, int32_t stride, int32_t rows,
+                       const int32_t* __restrict__ row_of, const int32_t* __restrict__ ctx_lens, int32_t block_size,
+                       int32_t* __restrict__ step_table, int32_t step_stride) {
+  const int j = blockIdx.x;
+  const int r = __ldg(row_of + j);
+  if ((unsigned)r >= (unsigned)rows) return;
+  const int len = max(__ldg(ctx_lens + j), 0);
+  const int n = min(min((len + block_size - 1) / block_size, stride), step_stride);
+  const int32_t* src = table + (int64_t)r * stride;
+  int32_t* dst = step_table + (int64_t)j * step_stride;
+  for (int c = threadIdx.x; c < n; c += blockDim.x) dst[c] = src[c];
+}
+
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 }  // namespace
@@ -144,6 +177,27 @@ extern "C" int pa_slot_mapping(const int32_t* block_table, int32_t start_pos, in
   if (!block_table || !slots) return PA_ERR_BAD_ARG;
   pa_slot_mapping_kernel<<<(num_tokens + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       block_table, start_pos, num_tokens, block_size, slots);
+  return cudaGetLastError() == cudaSuccess ? PA_OK : PA_ERR_CUDA;
+}
+
+extern "C" int pa_block_table_step(int32_t* table, int32_t table_stride, int32_t num_rows,
+                                   const int32_t* updates, const int32_t* num_updates, int32_t max_updates,
+                                   const int32_t* row_of, const int32_t* ctx_lens, int32_t num_gather,
+                                   int32_t block_size, int32_t* step_table, int32_t step_stride, void* stream) {
+  if (table_stride <= 0 || num_rows <= 0 || max_updates < 0 || num_gather < 0 || block_size <= 0) return PA_ERR_BAD_ARG;
+  if (!table) return PA_ERR_BAD_ARG;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (max_updates > 0) {
+    if (!updates || !num_updates) return PA_ERR_BAD_ARG;
+    int ctas = (max_updates + 255) / 256;
+    if (ctas > 64) ctas = 64;
+    pa_table_update_kernel<<<ctas, 256, 0, st>>>(table, table_stride, num_rows, updates, num_updates, max_updates);
+  }
+  if (num_gather > 0) {
+    if (!row_of || !ctx_lens || !step_table || step_stride <= 0) return PA_ERR_BAD_ARG;
+    pa_table_gather_kernel<<<num_gather, 128, 0, st>>>(table, table_stride, num_rows, row_of, ctx_lens, block_size,
+                                                       step_table, step_stride);
+  }
   return cudaGetLastError() == cudaSuccess ? PA_OK : PA_ERR_CUDA;
 }
 

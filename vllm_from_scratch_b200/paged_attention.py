@@ -220,6 +220,45 @@ def compute_slot_mapping_device(block_table: torch.Tensor, start_pos: int, num_t
     return slots
 
 
+def block_table_step(table: torch.Tensor, updates: Optional[torch.Tensor], num_updates: Optional[torch.Tensor],
+                     row_of: Optional[torch.Tensor], ctx_lens: Optional[torch.Tensor],
+                     step_table: Optional[torch.Tensor], block_size: int) -> None:
+    """One engine step of the persistent device block tables (``pa_block_table_step``; replaces the
+    per-step rebuild mini_vllm.py:729-739).  ``table`` int32 ``[rows, W]`` stays on the device across
+    steps; ``updates`` int32 ``[cap, 3]`` holds the scheduler's delta as (row, column, block id) triples
+    of which the first ``num_updates[0]`` (a DEVICE int32) are applied; then
+    ``step_table[j, :n] = table[row_of[j], :n]`` with ``n = ceil(ctx_lens[j] / block_size)`` for every
+    ``j < len(row_of)`` (``row_of[j] < 0`` leaves row j alone).  No host sync; graph-capturable."""
+    _require_cuda(table, "table")
+    if table.dtype != torch.int32 or table.dim() != 2 or table.stride(1) != 1:
+        raise ValueError("table must be int32 [rows, W] with a contiguous last axis")
+    max_upd = 0
+    upd_ptr = nupd_ptr = row_ptr = len_ptr = st_ptr = 0
+    if updates is not None and updates.numel():
+        _require_cuda(updates, "updates")
+        _require_cuda(num_updates, "num_updates")
+        if updates.dtype != torch.int32 or num_updates.dtype != torch.int32 or not updates.is_contiguous():
+            raise ValueError("updates must be contiguous int32 [cap, 3] and num_updates an int32 device tensor")
+        max_upd = updates.numel() // 3
+        upd_ptr, nupd_ptr = updates.data_ptr(), num_updates.data_ptr()
+    n_gather, st_stride = 0, 0
+    if row_of is not None and row_of.numel():
+        for name, ten in (("row_of", row_of), ("ctx_lens", ctx_lens), ("step_table", step_table)):
+            _require_cuda(ten, name)
+            if ten.dtype != torch.int32:
+                raise ValueError(f"{name} must be int32")
+        n_gather = row_of.numel()
+        if ctx_lens.numel() != n_gather or step_table.dim() != 2 or step_table.shape[0] < n_gather \
+                or step_table.stride(1) != 1 or not row_of.is_contiguous() or not ctx_lens.is_contiguous():
+            raise ValueError("row_of / ctx_lens must be contiguous [n] and step_table [>= n, W]")
+        row_ptr, len_ptr, st_ptr, st_stride = row_of.data_ptr(), ctx_lens.data_ptr(), step_table.data_ptr(), step_table.stride(0)
+    with _DeviceOf(table):
+        rc = _lib.load().pa_block_table_step(table.data_ptr(), table.stride(0), table.shape[0], upd_ptr, nupd_ptr,
+                                             max_upd, row_ptr, len_ptr, n_gather, block_size, st_ptr, st_stride,
+                                             _stream_ptr())
+    _lib.check(rc, "pa_block_table_step")
+
+
 # ---------------------------------------------------------------------------------------
 # KV slot write
 # ---------------------------------------------------------------------------------------
