@@ -229,6 +229,7 @@ def test_tiny_engine_cuda_bf16_fast_path():
 
     class Checked:
         reshape_and_cache = staticmethod(P.reshape_and_cache)
+        block_table_step = staticmethod(P.block_table_step)
 
         @staticmethod
         def paged_attention_decode_batched(q, cache, bts, lens):
@@ -262,6 +263,7 @@ def test_tiny_engine_cuda_bf16_varlen_one_launch():
 
     class Varlen:
         reshape_and_cache = staticmethod(P.reshape_and_cache)
+        block_table_step = staticmethod(P.block_table_step)
         prefill_tensor_core_available = staticmethod(P.prefill_tensor_core_available)
 
         @staticmethod
@@ -280,6 +282,7 @@ def test_tiny_engine_cuda_bf16_varlen_one_launch():
 
     class TwoKernel:
         reshape_and_cache = staticmethod(P.reshape_and_cache)
+        block_table_step = staticmethod(P.block_table_step)
         paged_attention_decode_batched = staticmethod(P.paged_attention_decode_batched)
         paged_attention_prefill_chunk = staticmethod(P.paged_attention_prefill_chunk)
 
@@ -302,6 +305,7 @@ def test_tiny_engine_cuda_bf16_split_route_for_decode_heavy_mixed_steps(monkeypa
 
     class Checked:
         reshape_and_cache = staticmethod(P.reshape_and_cache)
+        block_table_step = staticmethod(P.block_table_step)
         prefill_tensor_core_available = staticmethod(P.prefill_tensor_core_available)
         paged_attention_decode_batched = staticmethod(P.paged_attention_decode_batched)
 
@@ -316,8 +320,8 @@ def test_tiny_engine_cuda_bf16_split_route_for_decode_heavy_mixed_steps(monkeypa
 
     orig_attend = engine_adapter._attend
 
-    def attend(attn, ops, md, q, cache, t, h, d):
-        y = orig_attend(attn, ops, md, q, cache, t, h, d)
+    def attend(attn, ops, state, md, q, cache, t, h, d):
+        y = orig_attend(attn, ops, state, md, q, cache, t, h, d)
         if getattr(Checked, "pending", None) is not None:
             qq, cc, bts, cu, max_q, out = Checked.pending
             Checked.pending = None
