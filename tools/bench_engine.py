@@ -43,10 +43,10 @@ def prompts():
     return out
 
 
-def run_tiny(device, ops, dtype, hidden, heads, blocks, label):
+def run_tiny(device, ops, dtype, hidden, heads, blocks, label, graphs=None):
     eng = TinyEngine(vocab=1000, hidden=hidden, layers=4, heads=heads, inter=4 * hidden, num_blocks=blocks, block_size=16,
                      max_seqs=16, token_budget=64, device=device, dtype=dtype, hashed_blocks=True)
-    engine_adapter.install(eng, ops=ops)
+    engine_adapter.install(eng, ops=ops, cuda_graphs=graphs)
     mgr = kv_manager.install(eng, num_host_blocks=256, ops=ops)
     ps = prompts()
 
@@ -70,6 +70,9 @@ def run_tiny(device, ops, dtype, hidden, heads, blocks, label):
                       "heads": heads, "head_dim": hidden // heads, "kv_blocks": blocks, "requests": len(ps),
                       "input_tokens": in_tok, "output_tokens": out_tok, "steps": steps, "seconds": dt,
                       "output_tok_per_s": out_tok / dt, "total_tok_per_s": (in_tok + out_tok) / dt,
+                      "decode_graphs": None if eng._pa_b200["graphs"] is None else
+                      {"captures": eng._pa_b200["graphs"].captures, "replays": eng._pa_b200["graphs"].replays},
+                      "table_entries_shipped": eng._pa_b200["tables"].updates_sent,
                       "prefix_hit_tokens": mgr.stats.prefix_hit_tokens - before[0],
                       "preemptions": mgr.stats.preemptions - before[1],
                       "blocks_swapped_out": mgr.stats.blocks_swapped_out - before[2]}), flush=True)
@@ -102,5 +105,6 @@ if __name__ == "__main__":
         run_tiny("cpu", OracleOps, torch.float32, 256, 8, 40, "tiny_cpu_oracle")
         if torch.cuda.is_available():
             from vllm_from_scratch_b200 import paged_attention as P
-            run_tiny("cuda", P, torch.float32, 256, 8, 40, "tiny_cuda")
-            run_tiny("cuda", P, torch.bfloat16, 1024, 8, 40, "tiny_cuda")
+            for graphs in (False, True):
+                run_tiny("cuda", P, torch.float32, 256, 8, 40, "tiny_cuda", graphs)
+                run_tiny("cuda", P, torch.bfloat16, 1024, 8, 40, "tiny_cuda", graphs)

@@ -463,7 +463,17 @@ class DecodeGraphs:
         bucket = min(bucket, tables.cap)
         entry = self.graphs.get(bucket)
         if entry is None:
-            entry = self._capture(bucket)
+            # first decode-only step (or the mirror moved): capture EVERY bucket now, so that no later step
+            # stalls on a capture (~5 ms each, more when cuBLAS meets a new shape); padded requests are no-ops
+            # and the step's own K / V rows are written with the same values by each warm-up pass
+            k = 1
+            while k < tables.cap:
+                if k not in self.graphs:
+                    self._capture(k)
+                k *= 2
+            if tables.cap not in self.graphs:
+                self._capture(tables.cap)
+            entry = self.graphs[bucket]
         graph, logits = entry
         graph.replay()
         self.replays += 1
