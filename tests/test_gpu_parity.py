@@ -641,7 +641,7 @@ def test_abi_status_codes(lib):
     from vllm_from_scratch_b200._lib import PaKvCache
     import ctypes
     from vllm_from_scratch_b200 import _lib as L
-    assert lib.pa_abi_version() == L.ABI_VERSION == 2
+    assert lib.pa_abi_version() == L.ABI_VERSION == 3
     assert lib.pa_decode_num_workers() > 0
     c = PaKvCache(1, 1, 1, 1, 1, 1, 3, 16, 32, 0, 0)
     # Hq not a multiple of Hkv -> bad argument; never throws across the ABI

@@ -100,7 +100,7 @@ for combo in args.combos.split(","):
     print(f"units_per_sm={ups:3d} guided_k={gk} stages={st} claim={cl:3d}  {us:8.2f} us  {kvb / us / 1e3:8.1f} GB/s", flush=True)
     for k, v in tl.items():
         print(f"      {k:22s} {v}", flush=True)
-lib.pa_decode_set_tuning(16, 3, 0, 48)
+lib.pa_decode_set_tuning(16, 3, 0, 32)
 if args.out:
     os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
     json.dump({"workload": args.workload, "results": res}, open(args.out, "w"), indent=1)

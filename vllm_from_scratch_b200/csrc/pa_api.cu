@@ -18,7 +18,7 @@ std::atomic<int> g_force_path{0};
 std::atomic<int> g_units_per_sm{16};    // fast path: smallest split-K unit = total / (units_per_sm * SMs)
 std::atomic<int> g_guided_k{3};         // fast path: largest unit = remaining / (guided_k * SMs)
 std::atomic<int> g_stages{0};           // fast path: per-warp ring depth override (0 = as deep as fits)
-std::atomic<int> g_claim_limit{48};     // fast path: claim-ahead bound in blocks per CTA
+std::atomic<int> g_claim_limit{32};     // fast path: claim-ahead bound in blocks per CTA
 std::atomic<long long*> g_dbg{nullptr};
 
 int sm_count() {

@@ -61,12 +61,16 @@ constexpr int kBS = 16;             // tokens per block on this path
 constexpr int kConsumers = 8;       // consumer (math) warps per CTA: warps 0-7, two warpgroups
 constexpr int kProducers = 8;       // TMA producer warps, one per consumer: warps 8-15
 constexpr int kSchedWarp = kConsumers + kProducers;           // warp 16
-constexpr int kFinWarps = 3;        // finisher warps per CTA: warps 17-19, unit k of the CTA belongs to finisher k % 3
+constexpr int kFinWarps = 3;        // finisher warps per CTA: warp 17 merges units, warps 18-19 fold split segments together
+constexpr int kJobRing = 4;         // fold jobs in flight merger -> folders
                                     //   (scheduler + finishers = one warpgroup)
 constexpr int kThreads = (kConsumers + kProducers + 1 + kFinWarps) * 32;   // 640
 constexpr int kDescRing = 8;        // unit descriptors in flight scheduler -> producers / consumers
-constexpr int kNumBars = 2 * kConsumers * 8 /* kMaxStages */ + 3 * kDescRing + kFinWarps + 1;
-constexpr int kDescBlocks = 64;     // block-table entries per descriptor (longer units span several)
+constexpr int kNumBars = 2 * kConsumers * 8 /* kMaxStages */ + 3 * kDescRing + 2 + 2 * kJobRing;
+#ifndef PA_DESC_BLOCKS
+#define PA_DESC_BLOCKS 16
+#endif
+constexpr int kDescBlocks = PA_DESC_BLOCKS;   // blocks per descriptor (a unit spans several); a multiple of 8, 16 / 32 / 64
 constexpr int kMaxStages = 8;       // per-warp ring depth cap (kNumBars assumes 8)
 constexpr int kMaxPartials = 32;    // split-K partials per (sequence, KV head) segment, at most
 constexpr int kHeaderInts = 16;     // counter header: [0] unit ticket, [1] exited CTAs, [2] launch epoch
@@ -100,7 +104,7 @@ __host__ __device__ inline SmemLayout smem_layout(int hd, int g, int r, int batc
   L.qring = o;     o += (uint32_t)kDescRing * g * hd * 2;
   L.bt = o;        o += kDescRing * kDescBlocks * 4;
   L.desc = o;      o += kDescRing * 32;
-  L.fin = o;       o += 32;                              // unit merge job (2 x int4)
+  L.fin = o;       o += 32 + kJobRing * 16;              // unit merge job (2 x int4) + fold job ring (int4 each)
   L.bars = o;      o += (uint32_t)kNumBars * 8;
   L.scratch = o;   o += 48 * 4;
   L.lens = o;      o += (uint32_t)batch * 4;
@@ -316,8 +320,10 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   const uint32_t bar_dfull = bar_empty + kConsumers * kMaxStages * 8;    // [kDescRing]
   const uint32_t bar_dempty = bar_dfull + kDescRing * 8;                 // [kDescRing]  8 consumers + 8 producers
   const uint32_t bar_qfull = bar_dempty + kDescRing * 8;                 // [kDescRing]
-  const uint32_t bar_mfull = bar_qfull + kDescRing * 8;                  // [kFinWarps] unit k's state handed to finisher k % 3 (8 warps arrive)
-  const uint32_t bar_mempty = bar_mfull + kFinWarps * 8;                 // hand-off area free again
+  const uint32_t bar_mfull = bar_qfull + kDescRing * 8;                  // a unit's state handed to the merger (8 warps arrive)
+  const uint32_t bar_mempty = bar_mfull + 8;                             // hand-off area free again
+  const uint32_t bar_jfull = bar_mempty + 8;                             // [kJobRing] fold job posted
+  const uint32_t bar_jempty = bar_jfull + kJobRing * 8;                  // [kJobRing] read by both folders
   const uint32_t q_bytes = (uint32_t)g * HD * 2;
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -337,7 +343,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   // threads x 96 registers = 61440 - not the SM's 64 Ki (asking for more blocks forever).  The producers'
   // single active lane needs next to nothing; what they give back goes to the consumers (fragments of Q,
   // the O accumulator, K / V fragment sets in flight) and to the finishers (8 partials' loads in flight per
-  // lane): 256 x 144 + 256 x 40 + 128 x 112 = 61440.
+  // lane): 256 x 144 + 256 x 32 + 128 x 128 = 61440.
   // Each role's code sits entirely inside the branch that executes its setmaxnreg (ptxas only grants the
   // larger budget to code dominated by the instruction), so the one CTA-wide barrier is issued per branch.
   auto cta_sync = [] { asm volatile("bar.sync 0, %0;" ::"n"(kThreads) : "memory"); };
@@ -347,7 +353,8 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     const uint32_t b = bar_full + i * 8;
     uint32_t count = 1;
     if (b >= bar_dempty && b < bar_qfull) count = kConsumers + kProducers;
-    if (b >= bar_mfull && b < bar_mempty) count = kConsumers;   // every other barrier has ONE arriving thread
+    if (b >= bar_mfull && b < bar_mempty) count = kConsumers;
+    if (b >= bar_jempty) count = 2;                             // every other barrier has ONE arriving thread
     mbar_init(b, count);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -368,7 +375,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   __nv_bfloat16* obase = static_cast<__nv_bfloat16*>(p.out);
 
   if (warp >= kSchedWarp) {
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
   if (warp == kSchedWarp) {
     // =========================== scheduler warp ==========================================
     // The plan and the first unit are prepared BEFORE the CTA-wide barrier below: nothing here needs the
@@ -386,13 +393,16 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     build_plan(p.seq_lens, p.batch, hs, p.target_units, p.guided_k * (int)gridDim.x, s_len, s_c, s_ucum, lane);
     const int NU = s_ucum[p.batch] * hs;
     if (lane == 0) dbg_stamp(6);                                       // plan built
-    // One unit of look-ahead: `nx_*` is claimed, located and has its first 64 block-table entries
-    // in flight while the current unit is being published.
+    // `nx_*`: the unit claimed next - located, with its first 64 block-table entries in registers.  A ticket is
+    // claimed only when the CTA's backlog (blocks published but not yet consumed + blocks of the current unit
+    // not yet published) has become short: every ticket a CTA holds beyond what keeps its TMA rings busy is
+    // work the other SMs cannot take at the tail of the kernel (round 1 / early round 2 claimed two units
+    // ahead: the consumers' end times spread over 7 us = 1.3 tail units).
     int nx_s = 0, nx_h = 0, nx_b0 = 0, nx_n = 0, nx_nch = 0, nx_t = 0, nx_c = 0, nx_bt0 = 0, nx_bt1 = 0;
-    auto setup_next = [&]() {
+    auto setup_next = [&](bool first) {
+      if (!first && lane == 0) tk = atomicAdd(ticket, 1);
       nx_t = __shfl_sync(FULL, tk, 0);
       if (nx_t >= NU) { nx_n = 0; if (lane == 0) dbg_stamp(9); return; }     // tickets exhausted
-      if (lane == 0) tk = atomicAdd(ticket, 1);
       const PaCursor cu = pa_locate(s_ucum, p.batch, hs, nx_t);     // (s, h, chunk, chunks)
       nx_s = cu.s; nx_h = cu.h; nx_c = cu.b; nx_nch = cu.n;
       const int C = s_c[cu.s];
@@ -402,7 +412,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       nx_bt0 = lane < nx_n ? __ldg(row + lane) : 0;
       nx_bt1 = lane + 32 < nx_n ? __ldg(row + lane + 32) : 0;
     };
-    setup_next();
+    setup_next(true);
     cta_sync();                                                // mbarriers are initialised
 
     // sequences with no tokens: defined result is zeros (the reference raises, paged_attention.py:93)
@@ -418,9 +428,6 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       }
     const __nv_bfloat16* qbase = static_cast<const __nv_bfloat16*>(p.q);
     int u = 0;                                                       // descriptors published so far
-    // Claim-ahead is bounded in BLOCKS: a unit is published (and the next ticket claimed) only when
-    // fewer than `claim_limit` published blocks are still unconsumed - enough to cover the ticket and
-    // block-table round trips, small enough that no CTA hoards work the others could be doing.
     int rel = 0, outstanding = 0;                                    // descriptors [rel, u) not known released
     int* const hist = scratch;                                       // blocks of descriptor slot i
     auto wait_release = [&]() {
@@ -429,25 +436,38 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       outstanding -= hist[rel % kDescRing];
       ++rel;
     };
-    while (nx_n > 0) {
-      const int cs = nx_s, ch = nx_h, b0 = nx_b0, n = nx_n, nch = nx_nch, t = nx_t, c = nx_c;
-      int bt0 = nx_bt0, bt1 = nx_bt1;
-      while (rel < u && outstanding + min(n, kDescBlocks) > p.claim_limit) wait_release();
-      const int len = s_len[cs];
-      const int last_valid = (b0 + n == pa_ceil_div(len, kBS)) ? len - (b0 + n - 1) * kBS : kBS;
-      for (int j0 = 0; j0 < n; j0 += kDescBlocks) {
+    // A unit is published in descriptors of <= kDescBlocks blocks, one at a time, while fewer than `claim_limit`
+    // published blocks are unconsumed: deep enough to keep the 8 x R stage rings full, shallow enough that the
+    // release of one descriptor is a fine-grained progress signal.  The next ticket is claimed when the backlog
+    // (outstanding + unpublished rest of the current unit) drops below claim_limit + kDescBlocks.
+    const int pub_cap = p.claim_limit, claim_at = p.claim_limit + kDescBlocks;
+    int cs = 0, ch = 0, b0 = 0, n = 0, nch = 0, t = 0, c = 0, bt0 = 0, bt1 = 0, j0 = 0, last_valid = kBS;
+    bool have_cur = false, next_ready = true;                        // the first unit is already in nx_*
+    for (;;) {
+      const int unpub = have_cur ? n - j0 : 0;
+      if (!next_ready && outstanding + unpub < claim_at) {
+        setup_next(false);
+        next_ready = true;
+        continue;
+      }
+      if (have_cur) {
+        if (outstanding >= pub_cap || u - rel >= kDescRing) { wait_release(); continue; }
         const int nd = min(kDescBlocks, n - j0);
-        if (j0 > 0) {
+        const int o = j0 & 63;
+        if (o == 0 && j0 > 0) {                                      // the unit's next 64 block-table entries
           const int32_t* row = p.block_tables + (int64_t)cs * p.bt_stride + b0 + j0;
-          bt0 = lane < nd ? __ldg(row + lane) : 0;
-          bt1 = lane + 32 < nd ? __ldg(row + lane + 32) : 0;
+          bt0 = lane < n - j0 ? __ldg(row + lane) : 0;
+          bt1 = lane + 32 < n - j0 ? __ldg(row + lane + 32) : 0;
         }
         const int ds = u % kDescRing;
-        while (u - rel >= kDescRing) wait_release();                 // the slot's previous occupant is released
         hist[ds] = nd;
         outstanding += nd;
-        bt_ring[ds * kDescBlocks + lane] = bt0;
-        bt_ring[ds * kDescBlocks + lane + 32] = bt1;
+#pragma unroll
+        for (int i0 = 0; i0 < kDescBlocks; i0 += 32) {
+          const int e = o + i0 + lane;                               // entry of the 64-entry chunk
+          const int v0 = __shfl_sync(FULL, bt0, e & 31), v1 = __shfl_sync(FULL, bt1, e & 31);
+          if (i0 + lane < kDescBlocks) bt_ring[ds * kDescBlocks + i0 + lane] = (e & 32) ? v1 : v0;
+        }
         __syncwarp();
         if (lane == 0) {
           UnitDesc d;
@@ -466,8 +486,18 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
           }
         }
         ++u;
+        j0 += nd;
+        if (j0 == n) have_cur = false;
+        continue;
       }
-      setup_next();
+      if (!next_ready) { wait_release(); continue; }                 // backlog still long: wait for consumption
+      if (nx_n == 0) break;                                          // tickets exhausted, everything published
+      cs = nx_s; ch = nx_h; b0 = nx_b0; n = nx_n; nch = nx_nch; t = nx_t; c = nx_c; bt0 = nx_bt0; bt1 = nx_bt1;
+      const int len = s_len[cs];
+      last_valid = (b0 + n == pa_ceil_div(len, kBS)) ? len - (b0 + n - 1) * kBS : kBS;
+      j0 = 0;
+      have_cur = true;
+      next_ready = false;
     }
     while (u - rel >= kDescRing) wait_release();
     if (lane == 0) {
@@ -487,139 +517,190 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     // =========================== finisher warps ==========================================
     pdl_wait();
     cta_sync();                                                // mbarriers are initialised
-    // Unit k of this CTA (in the order the consumers finish them) belongs to finisher warp k % 3.  The warp merges
-    // the 8 consumer warps' (m, l, O) from the hand-off area and frees the area at once - the consumers only ever
-    // wait for THIS part.  A unit that is its segment's only one is normalised and written to `out`.  Any other
-    // unit's merged state goes to the unit's partial slot as self-validating 16-byte words {value, flag, value,
-    // flag} (flag = this launch's epoch): plain stores, no fence.  The unit also checks in at its segment's
-    // counter, and the warp whose unit is the last to check in folds the segment's partials in chunk order,
-    // polling each word until its flag shows this launch, and writes `out`.  The tail of a segment is therefore
-    // [hand-off + check-in, overlapped] -> one L2 round trip per partial -> stores; no fence sits in the chain
-    // (each costs microseconds while the SMs saturate HBM) and no warp ever waits for work that has not already
-    // reached its finisher.  Everything a lane folds is private to the lane (its value pairs, and its own copy
-    // of the heads' (m, l)), so the fold needs no shared memory and no warp-level synchronisation; the result
-    // does not depend on which warp folds.
+    // Warp 17, the MERGER, takes the units of the CTA in the order the consumers finish them: it merges the 8
+    // consumer warps' (m, l, O) from the hand-off area and frees the area at once - the consumers only ever wait
+    // for THIS part, ~0.3 us per unit (per-head weights are computed once, not per element).  A unit that is its
+    // segment's only one is normalised and written to `out`.  Any other unit's merged state goes to the unit's
+    // partial slot as self-validating 16-byte words {value, flag, value, flag} (flag = this launch's epoch):
+    // plain stores, no fence.  The unit also checks in at its segment's counter (the round trip hides behind the
+    // merge), and when it is the last to check in the merger posts a FOLD JOB and goes back to the hand-off.
+    // Warps 18 / 19, the FOLDERS, work on every fold job together, each on half of the GQA heads: they fold the
+    // segment's partials in chunk order with D partials' loads in flight per lane (one L2 round trip per D
+    // partials instead of one per partial), polling each word until its flag shows this launch, and write `out`.
+    // Earlier in round 2 each of three finisher warps did merge AND fold for "its" units: a fold of n partials
+    // was n dependent round trips (~0.7 us each while HBM is saturated) during which every third unit's hand-off
+    // stalled - the consumers of a CTA with 16 units waited 16 us for the hand-off area (32 units: 25 us).
+    // The result does not depend on which SM merges or folds: every element is folded in chunk order.
     const int fw = warp - kSchedWarp - 1;
     const int fli = scratch[kEpochSlot];
     const float flf = __int_as_float(fli);
     float4* const W = reinterpret_cast<float4*>(p.part_o);
+    int4* const jobs = mjob + 2;                                // [kJobRing] (s, h, nch, slot0); nch == 0: end of stream
     constexpr int WPR = HD / 2 + 1;                             // words per partial row: (m, l) + HD / 2 value pairs
-    constexpr int FU = 8;                                       // value words per lane in flight
-    constexpr int IPH = HD / 64;                                // consecutive items of a lane that share a head
-    const int nitems = g * (HD / 2);
-    auto ready = [&](const float4& w) { return __float_as_int(w.y) == fli && __float_as_int(w.w) == fli; };
-    for (int mi = fw;; mi += kFinWarps) {
-      mbar_wait(bar_mfull + fw * 8, (mi / kFinWarps) & 1);
-      const int4 j0 = mjob[0], j1 = mjob[1];
-      const int cs = j0.x, ch = j0.y, nch = j0.z, slot = j0.w, slot0 = j1.x, end = j1.y;
-      // Check in at the segment's counter FIRST: the round trip hides behind the merge below.  No fence is
-      // needed on either side of it - the count only elects the warp that folds the segment (the last to check
-      // in); the data that warp reads validates itself word by word.
-      int arrived = 0;
-      if (!end && nch > 1 && lane == 0) arrived = atomicAdd(seg_cnt + cs * hs + ch, 1);
-      if (!end) {
-        for (int e2 = lane; e2 < nitems; e2 += 32) {
-          const int head = e2 / (HD / 2), dp = (e2 - head * (HD / 2)) * 2;
-          float M = -INFINITY;
+    constexpr int IPH = HD / 64;                                // 32-element rows of value words per head
+    if (fw == 0) {
+      int njobs = 0;
+      auto post = [&](int4 job) {
+        const int js = njobs % kJobRing;
+        if (lane == 0) {
+          mbar_wait(bar_jempty + js * 8, ((njobs / kJobRing) & 1) ^ 1);
+          jobs[js] = job;
+          mbar_arrive(bar_jfull + js * 8);
+        }
+        ++njobs;
+      };
+      for (int mi = 0;; ++mi) {
+        mbar_wait(bar_mfull, mi & 1);
+        const int4 j0 = mjob[0], j1 = mjob[1];
+        const int cs = j0.x, ch = j0.y, nch = j0.z, slot = j0.w, slot0 = j1.x, end = j1.y;
+        // Check in at the segment's counter FIRST: the round trip hides behind the merge below.  No fence is
+        // needed on either side of it - the count only elects the unit that posts the fold (the last to check
+        // in); the data the folders read validates itself word by word.
+        int arrived = 0;
+        if (!end && nch > 1 && lane == 0) arrived = atomicAdd(seg_cnt + cs * hs + ch, 1);
+        if (!end) {
+          for (int head = 0; head < g; ++head) {
+            float mw[kConsumers], wg[kConsumers];
+            float M = -INFINITY, Lsum = 0.f;
 #pragma unroll
-          for (int w = 0; w < kConsumers; ++w) M = fmaxf(M, merge_ml[w * 8 + head].x);
-          float Lsum = 0.f, o0 = 0.f, o1 = 0.f;
-#pragma unroll
-          for (int w = 0; w < kConsumers; ++w) {
-            const float2 ml = merge_ml[w * 8 + head];
-            if (ml.x != -INFINITY) {
-              const float wg = exp2f(ml.x - M);
-              const float2 v = *reinterpret_cast<const float2*>(merge_o + (w * g + head) * OPITCH + dp);
-              Lsum = fmaf(ml.y, wg, Lsum);
-              o0 = fmaf(v.x, wg, o0);
-              o1 = fmaf(v.y, wg, o1);
+            for (int w = 0; w < kConsumers; ++w) {
+              const float2 ml = merge_ml[w * 8 + head];
+              mw[w] = ml.x;
+              wg[w] = ml.y;
+              M = fmaxf(M, ml.x);
             }
-          }
-          if (nch == 1) {
+#pragma unroll
+            for (int w = 0; w < kConsumers; ++w) {
+              const float l = wg[w];
+              wg[w] = 0.f;
+              if (mw[w] != -INFINITY) {
+                wg[w] = exp2f(mw[w] - M);
+                Lsum = fmaf(l, wg[w], Lsum);
+              }
+            }
             const float inv = 1.f / Lsum;
-            const int64_t off = (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + head) * p.o_stride_h + dp;
-            const uint32_t w0 = pack_bf16(o0 * inv, o1 * inv);
-            *reinterpret_cast<uint32_t*>(obase + off) = w0;
-            peer_store32(p, off, w0);
-          } else {
             float4* row = W + ((int64_t)slot * g + head) * WPR;
-            __stcg(row + 1 + (dp >> 1), make_float4(o0, flf, o1, flf));
-            if (dp == 0) __stcg(row, make_float4(M, flf, Lsum, flf));
+#pragma unroll
+            for (int r = 0; r < IPH; ++r) {
+              const int dp = (r * 32 + lane) * 2;
+              float o0 = 0.f, o1 = 0.f;
+#pragma unroll
+              for (int w = 0; w < kConsumers; ++w) {
+                if (mw[w] != -INFINITY) {                       // a warp without blocks left its rows unwritten
+                  const float2 v = *reinterpret_cast<const float2*>(merge_o + (w * g + head) * OPITCH + dp);
+                  o0 = fmaf(v.x, wg[w], o0);
+                  o1 = fmaf(v.y, wg[w], o1);
+                }
+              }
+              if (nch == 1) {
+                const int64_t off = (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + head) * p.o_stride_h + dp;
+                const uint32_t w0 = pack_bf16(o0 * inv, o1 * inv);
+                *reinterpret_cast<uint32_t*>(obase + off) = w0;
+                peer_store32(p, off, w0);
+              } else {
+                __stcg(row + 1 + (dp >> 1), make_float4(o0, flf, o1, flf));
+                if (dp == 0) __stcg(row, make_float4(M, flf, Lsum, flf));
+              }
+            }
           }
         }
+        __syncwarp();                                             // hand-off area read
+        if (lane == 0) mbar_arrive(bar_mempty);                   // the consumers may drop their next unit (or end marker)
+        if (end) {
+          post(make_int4(0, 0, 0, 0));
+          break;
+        }
+        if (nch == 1) {
+          if (lane == 0) peer_signal(p, 1u);                      // whole segment in one unit: its rows are stored
+          continue;
+        }
+        if (__shfl_sync(FULL, arrived, 0) != nch - 1) continue;
+        // last unit of the segment to check in: the others' stores were issued before or within about a
+        // microsecond of this point
+        if (lane == 0) seg_cnt[cs * hs + ch] = 0;                 // self-cleaning: every unit of the segment has checked in
+        post(make_int4(cs, ch, nch, slot0));
       }
-      __syncwarp();                                             // hand-off area read
-      if (lane == 0) mbar_arrive(bar_mempty);                   // the consumers may drop their next unit (or end marker)
-      if (end) break;
-      if (nch == 1) {
-        if (lane == 0) peer_signal(p, 1u);                      // whole segment in one unit: its rows are stored
-        continue;
-      }
-      if (__shfl_sync(FULL, arrived, 0) != nch - 1) continue;
-      // ---- last unit of the segment to check in: fold the nch partials in chunk order.  The others' stores
-      //      were issued before or within about a microsecond of this point; each word is polled until its
-      //      flag shows this launch. ----
-      if (lane == 0) seg_cnt[cs * hs + ch] = 0;                 // self-cleaning: every unit of the segment has checked in
-      for (int e0 = 0; e0 < nitems; e0 += 32 * FU) {
-        float M[FU / IPH], Ls[FU / IPH], o[FU][2];
+    } else {
+      constexpr int FU = 4;                                       // rows (value words per lane) of one pass
+      constexpr int HPG = FU / IPH;                               // heads of one pass
+      constexpr int DEPTH = HD == 128 ? 4 : 3;                    // partials in flight per lane: DEPTH * (FU + HPG) words
+      const int h0 = fw == 1 ? 0 : (g + 1) / 2, h1 = fw == 1 ? (g + 1) / 2 : g;   // this folder's GQA heads
+      auto ready = [&](const float4& w) { return __float_as_int(w.y) == fli && __float_as_int(w.w) == fli; };
+      for (int j = 0;; ++j) {
+        const int js = j % kJobRing;
+        mbar_wait(bar_jfull + js * 8, (j / kJobRing) & 1);
+        const int4 job = jobs[js];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_jempty + js * 8);
+        const int cs = job.x, ch = job.y, nch = job.z, slot0 = job.w;
+        if (nch == 0) break;
+        for (int hg = h0; hg < h1; hg += HPG) {
+          float M[HPG], Ls[HPG], o[FU][2];
 #pragma unroll
-        for (int h = 0; h < FU / IPH; ++h) { M[h] = -INFINITY; Ls[h] = 0.f; }
+          for (int h = 0; h < HPG; ++h) { M[h] = -INFINITY; Ls[h] = 0.f; }
 #pragma unroll
-        for (int u = 0; u < FU; ++u) o[u][0] = o[u][1] = 0.f;
-        const int head0 = (e0 + lane) / (HD / 2);               // item u of this batch belongs to head0 + u / IPH
-        const int idx0 = (e0 + lane) - head0 * (HD / 2);        //   and is value word idx0 + 32 * (u % IPH) of its row
-        for (int k = 0; k < nch; ++k) {
-          const float4* const base = W + (int64_t)(slot0 + k) * g * WPR;
-          float4 wv[FU], wm[FU / IPH];
+          for (int u = 0; u < FU; ++u) o[u][0] = o[u][1] = 0.f;
+          for (int k0 = 0; k0 < nch; k0 += DEPTH) {
+            float4 wv[DEPTH][FU], wm[DEPTH][HPG];
 #pragma unroll
-          for (int u = 0; u < FU; ++u) {
-            const int head = head0 + u / IPH;
-            const float4* src = base + (int64_t)head * WPR;
-            wv[u] = make_float4(0.f, flf, 0.f, flf);
-            if (u % IPH == 0) wm[u / IPH] = make_float4(-INFINITY, flf, 0.f, flf);
-            if (head < g) {
-              wv[u] = ld_poll(src + 1 + idx0 + 32 * (u % IPH));
-              if (u % IPH == 0) wm[u / IPH] = ld_poll(src);
+            for (int d = 0; d < DEPTH; ++d) {
+              const float4* const base = W + (int64_t)(slot0 + k0 + d) * g * WPR;
+#pragma unroll
+              for (int u = 0; u < FU; ++u) {
+                const int head = hg + u / IPH;
+                wv[d][u] = make_float4(0.f, flf, 0.f, flf);
+                if (u % IPH == 0) wm[d][u / IPH] = make_float4(-INFINITY, flf, 0.f, flf);
+                if (head < h1 && k0 + d < nch) {
+                  const float4* src = base + (int64_t)head * WPR;
+                  wv[d][u] = ld_poll(src + 1 + (u % IPH) * 32 + lane);
+                  if (u % IPH == 0) wm[d][u / IPH] = ld_poll(src);
+                }
+              }
+            }
+#pragma unroll
+            for (int d = 0; d < DEPTH; ++d) {
+              if (k0 + d < nch) {
+                const float4* const base = W + (int64_t)(slot0 + k0 + d) * g * WPR;
+#pragma unroll
+                for (int u = 0; u < FU; ++u) {
+                  const float4* src = base + (int64_t)(hg + u / IPH) * WPR;
+                  while (!ready(wv[d][u])) wv[d][u] = ld_poll(src + 1 + (u % IPH) * 32 + lane);
+                  if (u % IPH == 0)
+                    while (!ready(wm[d][u / IPH])) wm[d][u / IPH] = ld_poll(src);
+                }
+#pragma unroll
+                for (int h = 0; h < HPG; ++h) {
+                  // every partial holds >= 1 valid token (finite maximum); a head beyond h1 keeps weight 0
+                  const float Mn = fmaxf(M[h], wm[d][h].x);
+                  const float a = Mn == -INFINITY ? 0.f : exp2f(M[h] - Mn);
+                  const float bw = Mn == -INFINITY ? 0.f : exp2f(wm[d][h].x - Mn);
+                  Ls[h] = Ls[h] * a + wm[d][h].z * bw;
+                  M[h] = Mn;
+#pragma unroll
+                  for (int i = 0; i < IPH; ++i) {
+                    o[h * IPH + i][0] = o[h * IPH + i][0] * a + wv[d][h * IPH + i].x * bw;
+                    o[h * IPH + i][1] = o[h * IPH + i][1] * a + wv[d][h * IPH + i].z * bw;
+                  }
+                }
+              }
             }
           }
 #pragma unroll
           for (int u = 0; u < FU; ++u) {
-            const int head = head0 + u / IPH;
-            const float4* src = base + (int64_t)head * WPR;
-            while (!ready(wv[u])) wv[u] = ld_poll(src + 1 + idx0 + 32 * (u % IPH));
-            if (u % IPH == 0)
-              while (!ready(wm[u / IPH])) wm[u / IPH] = ld_poll(src);
-          }
-#pragma unroll
-          for (int h = 0; h < FU / IPH; ++h) {
-            // every partial holds >= 1 valid token (finite maximum); a head beyond g keeps weight 0
-            const float Mn = fmaxf(M[h], wm[h].x);
-            const float a = Mn == -INFINITY ? 0.f : exp2f(M[h] - Mn);
-            const float bw = Mn == -INFINITY ? 0.f : exp2f(wm[h].x - Mn);
-            Ls[h] = Ls[h] * a + wm[h].z * bw;
-            M[h] = Mn;
-#pragma unroll
-            for (int i = 0; i < IPH; ++i) {
-              o[h * IPH + i][0] = o[h * IPH + i][0] * a + wv[h * IPH + i].x * bw;
-              o[h * IPH + i][1] = o[h * IPH + i][1] * a + wv[h * IPH + i].z * bw;
+            const int head = hg + u / IPH;
+            if (head < h1) {
+              const float inv = 1.f / Ls[u / IPH];
+              const int dp = ((u % IPH) * 32 + lane) * 2;
+              const int64_t off = (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + head) * p.o_stride_h + dp;
+              const uint32_t w0 = pack_bf16(o[u][0] * inv, o[u][1] * inv);
+              *reinterpret_cast<uint32_t*>(obase + off) = w0;
+              peer_store32(p, off, w0);
             }
           }
         }
-#pragma unroll
-        for (int u = 0; u < FU; ++u) {
-          const int head = head0 + u / IPH;
-          if (head < g) {
-            const float inv = 1.f / Ls[u / IPH];
-            const int dp = (idx0 + 32 * (u % IPH)) * 2;
-            const int64_t off = (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + head) * p.o_stride_h + dp;
-            const uint32_t w0 = pack_bf16(o[u][0] * inv, o[u][1] * inv);
-            *reinterpret_cast<uint32_t*>(obase + off) = w0;
-            peer_store32(p, off, w0);
-          }
-        }
+        asm volatile("bar.sync 2, 64;" ::: "memory");             // both folders have stored their heads of the segment
+        if (fw == 1 && lane == 0) peer_signal(p, 1u);
       }
-      __syncwarp();
-      if (lane == 0) peer_signal(p, 1u);                        // after the warp-wide sync: all rows are stored
     }
     if (p.dbg && lane == 0) {                                   // the last of the three warps to leave
       unsigned long long t;
@@ -635,7 +716,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     // descriptor ring, takes the next free stage of the consumer's private ring and issues the block's two
     // tensor loads.  Waiting here - for a descriptor, for a free stage, or in the issue path itself when
     // the memory system pushes back - delays nobody's math.
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
     pdl_wait();
     cta_sync();                                                // mbarriers are initialised
     if (lane != 0) return;
@@ -857,16 +938,16 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       mjob[1] = make_int4(slot0, 0, 0, 0);
     }
     __syncwarp();
-    if (lane == 0) mbar_arrive(bar_mfull + (units_done % kFinWarps) * 8);
+    if (lane == 0) mbar_arrive(bar_mfull);
     ++units_done;
   }
-  // end of stream: one marker per finisher warp, through the same hand-off protocol
+  // end of stream: one marker for the merger (which passes it on to the folders), through the same hand-off protocol
   const int units_total = units_done;
-  for (int e = 0; e < kFinWarps; ++e) {
+  {
     mbar_wait(bar_mempty, (units_done & 1) ^ 1);
     if (threadIdx.x == 0) mjob[1] = make_int4(0, 1, 0, 0);
     __syncwarp();
-    if (lane == 0) mbar_arrive(bar_mfull + (units_done % kFinWarps) * 8);
+    if (lane == 0) mbar_arrive(bar_mfull);
     ++units_done;
   }
 
@@ -949,7 +1030,7 @@ int get_map(const void* base, const PaDecodeParams& p, CUtensorMap* out, int* po
   key.nb = p.num_blocks;
   if (cudaGetDevice(&key.dev) != cudaSuccess) { cudaGetLastError(); key.dev = -1; }
   static_assert(sizeof(MapKey) % 8 == 0, "hashed as 64-bit words");
-  static_assert(kThreads * 96 == 256 * 144 + 256 * 40 + 128 * 112, "setmaxnreg budgets must add up to the launch allocation");
+  static_assert(kThreads * 96 == 256 * 144 + 256 * 32 + 128 * 128, "setmaxnreg budgets must add up to the launch allocation");
   std::lock_guard<std::mutex> lock(g_map_mu);
   MapEntry* set = g_maps + (map_hash(key) % kMapSets) * kMapWays;
   MapEntry* victim = set;
