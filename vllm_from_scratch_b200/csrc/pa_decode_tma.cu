@@ -62,7 +62,7 @@ constexpr int kConsumers = 8;       // consumer (math) warps per CTA: warps 0-7,
 constexpr int kProducers = 8;       // TMA producer warps, one per consumer: warps 8-15
 constexpr int kSchedWarp = kConsumers + kProducers;           // warp 16
 constexpr int kFinWarps = 3;        // finisher warps per CTA: warp 17 merges units, warps 18-19 fold split segments together
-constexpr int kJobRing = 4;         // fold jobs in flight merger -> folders
+constexpr int kJobRing = 32;        // fold jobs in flight merger -> folders (a CTA has a handful pending; see the merger)
                                     //   (scheduler + finishers = one warpgroup)
 constexpr int kThreads = (kConsumers + kProducers + 1 + kFinWarps) * 32;   // 640
 constexpr int kDescRing = 8;        // unit descriptors in flight scheduler -> producers / consumers
@@ -371,7 +371,6 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   };
   const int hs = p.num_kv_heads;
   int* const ticket = p.counters;                            // [0] unit ticket, [1] exited CTAs, [2] launch epoch
-  int* const seg_cnt = p.counters + kHeaderInts;             // [segment] units checked in; zero between launches
   __nv_bfloat16* obase = static_cast<__nv_bfloat16*>(p.out);
 
   if (warp >= kSchedWarp) {
@@ -553,11 +552,6 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
         mbar_wait(bar_mfull, mi & 1);
         const int4 j0 = mjob[0], j1 = mjob[1];
         const int cs = j0.x, ch = j0.y, nch = j0.z, slot = j0.w, slot0 = j1.x, end = j1.y;
-        // Check in at the segment's counter FIRST: the round trip hides behind the merge below.  No fence is
-        // needed on either side of it - the count only elects the unit that posts the fold (the last to check
-        // in); the data the folders read validates itself word by word.
-        int arrived = 0;
-        if (!end && nch > 1 && lane == 0) arrived = atomicAdd(seg_cnt + cs * hs + ch, 1);
         if (!end) {
           for (int head = 0; head < g; ++head) {
             float mw[kConsumers], wg[kConsumers];
@@ -614,11 +608,13 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
           if (lane == 0) peer_signal(p, 1u);                      // whole segment in one unit: its rows are stored
           continue;
         }
-        if (__shfl_sync(FULL, arrived, 0) != nch - 1) continue;
-        // last unit of the segment to check in: the others' stores were issued before or within about a
-        // microsecond of this point
-        if (lane == 0) seg_cnt[cs * hs + ch] = 0;                 // self-cleaning: every unit of the segment has checked in
-        post(make_int4(cs, ch, nch, slot0));
+        // The CTA that ran a split segment's FIRST unit folds the segment: its folders start polling the partial
+        // slots right away and finish one L2 round trip after the last partial lands.  (Electing the LAST unit to
+        // check in at an atomic counter - rounds 1 and early 2 - piles the folds of the final segments onto the
+        // few CTAs that finish last: with 16-block tail units one CTA folded for 13 us after its consumers' end.)
+        // Units of a segment hold consecutive tickets, so they are claimed by different CTAs at about the same
+        // time and the folds spread evenly over all SMs' folder warps.
+        if (slot == slot0) post(make_int4(cs, ch, nch, slot0));
       }
     } else {
       constexpr int FU = 4;                                       // rows (value words per lane) of one pass
@@ -664,9 +660,9 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
 #pragma unroll
                 for (int u = 0; u < FU; ++u) {
                   const float4* src = base + (int64_t)(hg + u / IPH) * WPR;
-                  while (!ready(wv[d][u])) wv[d][u] = ld_poll(src + 1 + (u % IPH) * 32 + lane);
+                  while (!ready(wv[d][u])) { __nanosleep(40); wv[d][u] = ld_poll(src + 1 + (u % IPH) * 32 + lane); }
                   if (u % IPH == 0)
-                    while (!ready(wm[d][u / IPH])) wm[d][u / IPH] = ld_poll(src);
+                    while (!ready(wm[d][u / IPH])) { __nanosleep(40); wm[d][u / IPH] = ld_poll(src); }
                 }
 #pragma unroll
                 for (int h = 0; h < HPG; ++h) {
