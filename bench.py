@@ -245,16 +245,24 @@ class Timer:
         if self.world > 1:
             self.dist.barrier()
 
-    def run(self, step, steps, lead=2, first=0):
+    def run(self, step, steps, lead=2, first=0, many=None):
+        """`many(first, n)` (optional) runs steps first .. first + n - 1 in as few launches as it can (e.g. one
+        CUDA graph holding a whole round of layer caches); the step count is the same either way."""
         torch = self.torch
         self.barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        for i in range(lead):
-            step(first + i)
+        if many is not None:
+            many(first, lead)
+        else:
+            for i in range(lead):
+                step(first + i)
         self.e0.record()
-        for i in range(steps):
-            step(first + lead + i)
+        if many is not None:
+            many(first + lead, steps)
+        else:
+            for i in range(steps):
+                step(first + lead + i)
         self.e1.record()
         torch.cuda.synchronize()
         t1 = time.perf_counter()
@@ -518,12 +526,30 @@ def run_ours(args):
     if peer_mode and layers % 2:
         raise SystemExit("--gather peer needs an even --layers (the two gather buffer sets alternate)")
     graphed = not (head_mode and not peer_mode)          # the NCCL arm stays eager (collective outside a graph)
+    step_many = None
     if graphed:
         if peer_mode:
             for i in range(2 * layers):                  # eager first, an even count: both buffer sets warm
                 step_eager(i)
         graphs = capture_steps(torch, step_eager, layers)
         step = lambda i: graphs[i % layers].replay()     # noqa: E731
+        if not head_mode:
+            # one more graph holding a whole round over the layer caches, in order: what an engine's decode step
+            # over its layers looks like - consecutive launches inside one graph keep their programmatic
+            # dependent-launch edges (the next kernel's prologue runs under the previous kernel's tail), which
+            # separate graph launches cannot.  The timed region still counts every kernel launch as one step;
+            # steps that do not fill a round are replayed from the per-layer graphs.
+            round_graph = capture_steps(torch, step_eager, layers, one_graph=True)[0]
+
+            def step_many(first, n):
+                i = first
+                while n > 0:
+                    if i % layers == 0 and n >= layers:
+                        round_graph.replay()
+                        i, n = i + layers, n - layers
+                    else:
+                        graphs[i % layers].replay()
+                        i, n = i + 1, n - 1
     else:
         step = step_eager
 
@@ -545,8 +571,8 @@ def run_ours(args):
     torch.cuda.synchronize()
 
     # ---- timed region: K steps, device time, max over ranks --------------------------------
-    lead = 2 * layers if peer_mode else 2
-    ms_total, t0, t1 = timer.run(step, args.steps, lead=lead)
+    lead = 2 * layers if peer_mode else (layers if step_many is not None else 2)
+    ms_total, t0, t1 = timer.run(step, args.steps, lead=lead, many=step_many)
     clocks = sampler.summary(t0, t1)
     if peer_mode and (args.steps % 2):                   # odd K: one more step realigns the buffer sets
         step(lead + args.steps)
@@ -647,7 +673,10 @@ def run_ours(args):
         "kv_read_gbs": kv_gbs, "kv_read_gbs_per_gpu": kv_gbs / world,
         "pct_of_8tbs_per_gpu": 100.0 * kv_gbs / world / NOMINAL_HBM_GBS,
         "kv_bytes_per_step_per_gpu": kv_bytes,
-        "launch_path": ("one CUDA graph per layer cache, replayed (captures exactly the eager step's launches)"
+        "launch_path": (("one CUDA graph per round over the layer caches (the eager steps' launches in order, programmatic "
+                         "dependent-launch edges kept), replayed; steps that do not fill a round from one graph per layer cache"
+                         if step_many is not None else
+                         "one CUDA graph per layer cache, replayed (captures exactly the eager step's launches)")
                         if graphed else "eager launches"),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(wl_name), "peak_source": peak_src,

@@ -42,7 +42,7 @@ def graph_time(fn, reps=LAYERS, iters=60):
     return ts[len(ts) // 2]
 
 
-for world in (1, 2, 4, 8):
+for world in [int(x) for x in os.environ.get("WORLDS", "1,2,4,8").split(",")]:
     b, ctx, d, bs = 8, 32768, 128, 16
     hkv, hq = 8 // world, 32 // world
     wl = (b, ctx, hq, hkv, d, bs, LAYERS, "")
@@ -60,7 +60,9 @@ for world in (1, 2, 4, 8):
             continue
         us = graph_time(lambda i: P.paged_attention_decode_batched(q, caches[i], bts, lens, out=out, workspace=ws))
         print(f"   units_per_sm={ups:3d} guided_k={gk} claim={cl:3d}: {us:7.1f} us  {kvb / us / 1e3:7.0f} GB/s", flush=True)
-    lib.pa_decode_set_tuning(16, 3, 0, 48)
+    lib.pa_decode_set_tuning(16, 3, 0, 32)
+    if os.environ.get("NO_PEER"):
+        continue
     pg = S.PeerGather(b, hq, hkv, d, dev, world=1, rank=0)
     us = graph_time(lambda i: pg.decode(q, caches[i], bts, lens, workspace=ws, parity=i % 2))
     print(f"   fused gather (world 1: local counters + wait kernel): {us:7.1f} us", flush=True)

@@ -49,7 +49,7 @@ WsLayout ws_layout(int batch, int64_t slots, int rows, int head_dim, bool flagge
   w.plan_off = kHeaderBytes;
   w.ml_off = w.plan_off + align_up((size_t)(batch + 3) * 4, 256);
   w.o_off = w.ml_off + align_up(flagged ? 0 : (size_t)slots * rows * sizeof(float2), 256);
-  w.total = w.o_off + align_up(flagged ? (size_t)slots * rows * (head_dim / 2 + 1) * 16
+  w.total = w.o_off + align_up(flagged ? 2 * (size_t)slots * rows * (head_dim / 2 + 1) * 16   // units' partials + level-2
                                        : (size_t)slots * rows * head_dim * sizeof(float), 256);
   return w;
 }
@@ -227,6 +227,7 @@ static int decode_impl(const void* q, int64_t q_stride_b, int64_t q_stride_h, vo
   p.plan = reinterpret_cast<int32_t*>(ws + w.plan_off);
   p.part_ml = reinterpret_cast<float2*>(ws + w.ml_off);
   p.part_o = reinterpret_cast<float*>(ws + w.o_off);
+  p.part_o2 = tma ? p.part_o + (size_t)slots * rows * (D / 2 + 1) * 4 : nullptr;
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaEvent_t* pe = nullptr;

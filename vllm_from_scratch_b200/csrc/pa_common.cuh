@@ -49,6 +49,7 @@ struct PaDecodeParams {
   float scale_log2e;      // (1 / sqrt(D)) * log2(e)
   // workspace
   float* part_o;          // [slots][tile_q][D]
+  float* part_o2;         // TMA path: second partial area of the same size (level-2 partials of two-level folds)
   float2* part_ml;        // [slots][tile_q]  (m in log2 domain, l)
   int32_t* plan;          // [0] = Q, [1] = total linear blocks, [2 .. 2 + B] = cum[0..B]  (generic path)
   int32_t* counters;      // zero-initialised counter header, left zero by every launch (TMA path)

@@ -62,6 +62,7 @@ constexpr int kConsumers = 8;       // consumer (math) warps per CTA: warps 0-7,
 constexpr int kProducers = 8;       // TMA producer warps, one per consumer: warps 8-15
 constexpr int kSchedWarp = kConsumers + kProducers;           // warp 16
 constexpr int kFinWarps = 3;        // finisher warps per CTA: warp 17 merges units, warps 18-19 fold split segments together
+constexpr int kFoldGroup = 8;       // segments of more partials are folded in two levels: groups of 8, then the groups
 constexpr int kJobRing = 32;        // fold jobs in flight merger -> folders (a CTA has a handful pending; see the merger)
                                     //   (scheduler + finishers = one warpgroup)
 constexpr int kThreads = (kConsumers + kProducers + 1 + kFinWarps) * 32;   // 640
@@ -534,6 +535,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     const int fli = scratch[kEpochSlot];
     const float flf = __int_as_float(fli);
     float4* const W = reinterpret_cast<float4*>(p.part_o);
+    float4* const W2 = reinterpret_cast<float4*>(p.part_o2);   // level-2 partials (folds of kFoldGroup partials)
     int4* const jobs = mjob + 2;                                // [kJobRing] (s, h, nch, slot0); nch == 0: end of stream
     constexpr int WPR = HD / 2 + 1;                             // words per partial row: (m, l) + HD / 2 value pairs
     constexpr int IPH = HD / 64;                                // 32-element rows of value words per head
@@ -614,7 +616,22 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
         // few CTAs that finish last: with 16-block tail units one CTA folded for 13 us after its consumers' end.)
         // Units of a segment hold consecutive tickets, so they are claimed by different CTAs at about the same
         // time and the folds spread evenly over all SMs' folder warps.
-        if (slot == slot0) post(make_int4(cs, ch, nch, slot0));
+        // A segment of more than kFoldGroup partials is folded in two levels (a fold of n partials costs n / DEPTH
+        // dependent L2 round trips on ONE warp pair): the CTA that ran chunk 8 j folds partials [8 j, 8 j + 8) into a
+        // level-2 partial (second half of the partial area, same slot index), and the last group's CTA folds those.
+        // job = (s, h, count | stride << 8 | source level << 16 | writes a level-2 partial << 17, first slot).
+        const int c = slot - slot0;
+        if (nch <= kFoldGroup) {
+          if (c == 0) post(make_int4(cs, ch, nch | (1 << 8), slot0));
+        } else if (c % kFoldGroup == 0) {
+          post(make_int4(cs, ch, min(kFoldGroup, nch - c) | (1 << 8) | (1 << 17), slot));
+          // The final fold belongs to the CTA of the LAST group: every job then depends only on units and on jobs
+          // posted for smaller tickets, and a CTA posts in ticket order, so its FIFO can never hold a job behind
+          // one that waits for it (with the chunk-0 CTA folding, a CTA that also ran chunk 8 of the same segment
+          // queued the group fold BEHIND the final fold that polls for its result: deadlock).
+          if (c + kFoldGroup >= nch)
+            post(make_int4(cs, ch, pa_ceil_div(nch, kFoldGroup) | (kFoldGroup << 8) | (1 << 16), slot0));
+        }
       }
     } else {
       constexpr int FU = 4;                                       // rows (value words per lane) of one pass
@@ -628,8 +645,10 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
         const int4 job = jobs[js];
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_jempty + js * 8);
-        const int cs = job.x, ch = job.y, nch = job.z, slot0 = job.w;
+        const int cs = job.x, ch = job.y, nch = job.z & 0xff, kstride = (job.z >> 8) & 0xff, slot0 = job.w;
+        const bool to_partial = (job.z >> 17) & 1;
         if (nch == 0) break;
+        const float4* const Wsrc = ((job.z >> 16) & 1) ? W2 : W;
         for (int hg = h0; hg < h1; hg += HPG) {
           float M[HPG], Ls[HPG], o[FU][2];
 #pragma unroll
@@ -640,7 +659,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
             float4 wv[DEPTH][FU], wm[DEPTH][HPG];
 #pragma unroll
             for (int d = 0; d < DEPTH; ++d) {
-              const float4* const base = W + (int64_t)(slot0 + k0 + d) * g * WPR;
+              const float4* const base = Wsrc + (int64_t)(slot0 + (k0 + d) * kstride) * g * WPR;
 #pragma unroll
               for (int u = 0; u < FU; ++u) {
                 const int head = hg + u / IPH;
@@ -656,7 +675,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
 #pragma unroll
             for (int d = 0; d < DEPTH; ++d) {
               if (k0 + d < nch) {
-                const float4* const base = W + (int64_t)(slot0 + k0 + d) * g * WPR;
+                const float4* const base = Wsrc + (int64_t)(slot0 + (k0 + d) * kstride) * g * WPR;
 #pragma unroll
                 for (int u = 0; u < FU; ++u) {
                   const float4* src = base + (int64_t)(hg + u / IPH) * WPR;
@@ -684,7 +703,11 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
 #pragma unroll
           for (int u = 0; u < FU; ++u) {
             const int head = hg + u / IPH;
-            if (head < h1) {
+            if (head < h1 && to_partial) {                      // level-2 partial: same row format as a unit's
+              float4* row = W2 + ((int64_t)slot0 * g + head) * WPR;
+              __stcg(row + 1 + (u % IPH) * 32 + lane, make_float4(o[u][0], flf, o[u][1], flf));
+              if (u % IPH == 0 && lane == 0) __stcg(row, make_float4(M[u / IPH], flf, Ls[u / IPH], flf));
+            } else if (head < h1) {
               const float inv = 1.f / Ls[u / IPH];
               const int dp = ((u % IPH) * 32 + lane) * 2;
               const int64_t off = (int64_t)cs * p.o_stride_b + (int64_t)(ch * g + head) * p.o_stride_h + dp;
@@ -694,8 +717,10 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
             }
           }
         }
-        asm volatile("bar.sync 2, 64;" ::: "memory");             // both folders have stored their heads of the segment
-        if (fw == 1 && lane == 0) peer_signal(p, 1u);
+        if (!to_partial && p.local_sig != nullptr) {
+          asm volatile("bar.sync 2, 64;" ::: "memory");           // both folders have stored their heads of the segment
+          if (fw == 1 && lane == 0) peer_signal(p, 1u);
+        }
       }
     }
     if (p.dbg && lane == 0) {                                   // the last of the three warps to leave
