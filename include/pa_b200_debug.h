@@ -30,7 +30,8 @@ int pa_decode_force_path(int path);
  * `remaining` blocks are left is about remaining / (guided_k * SMs) blocks (default 3), never
  * smaller than total / (units_per_sm * SMs) (1 .. 64, default 16).  stages: per-warp TMA ring
  * depth, 0 = as deep as shared memory allows.  claim_limit: a CTA claims its next unit
- * only while fewer than this many claimed KV blocks are unprocessed (default 48).        */
+ * only while its backlog (published-unconsumed + unpublished blocks) is below claim_limit + 16, and
+ * publishes a unit's 16-block descriptors only while fewer than claim_limit are unconsumed (default 32). */
 int pa_decode_set_tuning(int units_per_sm, int guided_k, int stages, int claim_limit);
 /* Launch the TMA decode kernel with programmatic stream serialisation (default on): back-to-back launches on
  * one stream overlap the next kernel's prologue with the previous kernel's tail.  Returns the old setting. */
@@ -38,7 +39,8 @@ int pa_decode_set_pdl(int on);
 /* Debug: when non-null, every fast-path CTA writes its timeline, 16 int64 at device_buffer[16 * cta]
  * (globaltimer ns): [0] SM id, [1] CTA start, [2] consumers' end, [3] units processed, [4] finishers'
  * end, [5] first KV block landed, [6] plan built, [7] first unit published, [8] first TMA load issued,
- * [9] ticket counter found exhausted; (SM cycles, consumer warp 0:) [13] waited for unit descriptors,
+ * [9] ticket counter found exhausted, [10] last unit merged, [11] last fold job taken by the folders, [12] its last
+ * batch of partials seen; (SM cycles, consumer warp 0:) [13] waited for unit descriptors,
  * [14] for KV data, [15] for the hand-off area to the finishers.  pa_decode_num_workers() entries.   */
 int pa_decode_debug_times(void* device_buffer);
 /* Same for the tcgen05 prefill kernel: 8 int64 per CTA (grid order x, y, z): SM id,

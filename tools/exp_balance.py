@@ -86,7 +86,12 @@ def timeline():
             # hand-off area to the finishers
             "cons_wait_desc_us": pct(r[:, 13] / 1965.0), "cons_wait_data_us": pct(r[:, 14] / 1965.0),
             "cons_wait_handoff_us": pct(r[:, 15] / 1965.0),
-            "units_per_cta": [int(r[:, 3].min()), int(np.median(r[:, 3])), int(r[:, 3].max())]}, np.stack(recs)
+            "units_per_cta": [int(r[:, 3].min()), int(np.median(r[:, 3])), int(r[:, 3].max())],
+            # the chain behind the slowest finishers: last unit merged, last fold job taken, its last batch seen, done
+            "slowest_finishers": [{"cta": int(i), "consumers_end": round(float(rel(2)[i]), 2),
+                                   "last_merge": round(float(rel(10)[i]), 2), "last_job_taken": round(float(rel(11)[i]), 2),
+                                   "last_batch_seen": round(float(rel(12)[i]), 2), "finisher_end": round(float(rel(4)[i]), 2)}
+                                  for i in np.argsort(-rel(4))[:4]]}, np.stack(recs)
 
 
 lib.pa_decode_set_pdl(args.pdl)

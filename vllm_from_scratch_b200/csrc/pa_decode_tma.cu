@@ -71,6 +71,9 @@ constexpr int kNumBars = 2 * kConsumers * 8 /* kMaxStages */ + 3 * kDescRing + 2
 #ifndef PA_DESC_BLOCKS
 #define PA_DESC_BLOCKS 16
 #endif
+#ifndef PA_FOLD_DEPTH
+#define PA_FOLD_DEPTH (HD == 128 ? 4 : 2)
+#endif
 constexpr int kDescBlocks = PA_DESC_BLOCKS;   // blocks per descriptor (a unit spans several); a multiple of 8, 16 / 32 / 64
 constexpr int kMaxStages = 8;       // per-warp ring depth cap (kNumBars assumes 8)
 constexpr int kMaxPartials = 32;    // split-K partials per (sequence, KV head) segment, at most
@@ -602,6 +605,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
         }
         __syncwarp();                                             // hand-off area read
         if (lane == 0) mbar_arrive(bar_mempty);                   // the consumers may drop their next unit (or end marker)
+        if (!end && lane == 0) dbg_stamp(10);                     // (last) unit merged
         if (end) {
           post(make_int4(0, 0, 0, 0));
           break;
@@ -636,7 +640,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     } else {
       constexpr int FU = 4;                                       // rows (value words per lane) of one pass
       constexpr int HPG = FU / IPH;                               // heads of one pass
-      constexpr int DEPTH = HD == 128 ? 4 : 3;                    // partials in flight per lane: DEPTH * (FU + HPG) words
+      constexpr int DEPTH = PA_FOLD_DEPTH;                    // partials in flight per lane: DEPTH * (FU + HPG) words
       const int h0 = fw == 1 ? 0 : (g + 1) / 2, h1 = fw == 1 ? (g + 1) / 2 : g;   // this folder's GQA heads
       auto ready = [&](const float4& w) { return __float_as_int(w.y) == fli && __float_as_int(w.w) == fli; };
       for (int j = 0;; ++j) {
@@ -648,6 +652,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
         const int cs = job.x, ch = job.y, nch = job.z & 0xff, kstride = (job.z >> 8) & 0xff, slot0 = job.w;
         const bool to_partial = (job.z >> 17) & 1;
         if (nch == 0) break;
+        if (fw == 1 && lane == 0) dbg_stamp(11);                  // (last) fold job taken
         const float4* const Wsrc = ((job.z >> 16) & 1) ? W2 : W;
         for (int hg = h0; hg < h1; hg += HPG) {
           float M[HPG], Ls[HPG], o[FU][2];
@@ -657,32 +662,52 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
           for (int u = 0; u < FU; ++u) o[u][0] = o[u][1] = 0.f;
           for (int k0 = 0; k0 < nch; k0 += DEPTH) {
             float4 wv[DEPTH][FU], wm[DEPTH][HPG];
+            // Wait for this batch of partials on ONE sentinel word per partial (lane d polls the LAST word its writer
+            // stores of the heads folded in this pass, partial k0 + d): the
+            // folders start polling long before the partials land, and a re-poll of every word of every partial
+            // would put terabytes per second of L2 traffic next to the KV stream.  (Re-polling word by word, as
+            // rounds 1 and early 2 did, is worse still: 24 dependent round trips per batch - a 13 us fold tail.)
+            for (;;) {
+              bool ok = true;
+              if (lane < DEPTH && k0 + lane < nch)
+                ok = ready(ld_poll(Wsrc + ((int64_t)(slot0 + (k0 + lane) * kstride) * g + min(hg + HPG, h1)) * WPR - 1));
+              if (__all_sync(FULL, ok)) break;
+              __nanosleep(100);
+            }
+            if (fw == 1 && lane == 0) dbg_stamp(12);              // (last) batch of partials seen
+            // all of the batch's words in flight at once; the stores of a partial are not ordered among
+            // themselves, so every word is validated and the whole batch is reloaded in the (rare) miss
+            for (;;) {
+              bool ok = true;
 #pragma unroll
-            for (int d = 0; d < DEPTH; ++d) {
-              const float4* const base = Wsrc + (int64_t)(slot0 + (k0 + d) * kstride) * g * WPR;
+              for (int d = 0; d < DEPTH; ++d) {
+                const float4* const base = Wsrc + (int64_t)(slot0 + (k0 + d) * kstride) * g * WPR;
 #pragma unroll
-              for (int u = 0; u < FU; ++u) {
-                const int head = hg + u / IPH;
-                wv[d][u] = make_float4(0.f, flf, 0.f, flf);
-                if (u % IPH == 0) wm[d][u / IPH] = make_float4(-INFINITY, flf, 0.f, flf);
-                if (head < h1 && k0 + d < nch) {
-                  const float4* src = base + (int64_t)head * WPR;
-                  wv[d][u] = ld_poll(src + 1 + (u % IPH) * 32 + lane);
-                  if (u % IPH == 0) wm[d][u / IPH] = ld_poll(src);
+                for (int u = 0; u < FU; ++u) {
+                  const int head = hg + u / IPH;
+                  wv[d][u] = make_float4(0.f, flf, 0.f, flf);
+                  if (u % IPH == 0) wm[d][u / IPH] = make_float4(-INFINITY, flf, 0.f, flf);
+                  if (head < h1 && k0 + d < nch) {
+                    const float4* src = base + (int64_t)head * WPR;
+                    wv[d][u] = ld_poll(src + 1 + (u % IPH) * 32 + lane);
+                    if (u % IPH == 0) wm[d][u / IPH] = ld_poll(src);
+                  }
                 }
               }
+#pragma unroll
+              for (int d = 0; d < DEPTH; ++d) {
+#pragma unroll
+                for (int u = 0; u < FU; ++u) {
+                  ok = ok && ready(wv[d][u]);
+                  if (u % IPH == 0) ok = ok && ready(wm[d][u / IPH]);
+                }
+              }
+              if (__all_sync(FULL, ok)) break;
+              __nanosleep(60);
             }
 #pragma unroll
             for (int d = 0; d < DEPTH; ++d) {
               if (k0 + d < nch) {
-                const float4* const base = Wsrc + (int64_t)(slot0 + (k0 + d) * kstride) * g * WPR;
-#pragma unroll
-                for (int u = 0; u < FU; ++u) {
-                  const float4* src = base + (int64_t)(hg + u / IPH) * WPR;
-                  while (!ready(wv[d][u])) { __nanosleep(40); wv[d][u] = ld_poll(src + 1 + (u % IPH) * 32 + lane); }
-                  if (u % IPH == 0)
-                    while (!ready(wm[d][u / IPH])) { __nanosleep(40); wm[d][u / IPH] = ld_poll(src); }
-                }
 #pragma unroll
                 for (int h = 0; h < HPG; ++h) {
                   // every partial holds >= 1 valid token (finite maximum); a head beyond h1 keeps weight 0
