@@ -24,7 +24,9 @@ int pa_prefill_force_path(int path);
 
 /* ---- test / tuning hook ---------------------------------------------------
  * 0 = automatic kernel choice (default); 1 = force the generic CUDA-core
- * decode kernel even for shapes the TMA kernel takes.  Returns the old value. */
+ * decode path even for shapes the TMA kernel takes (the cp.async streaming kernel where rows
+ * are 16-byte aligned); 2 = force the plain generic kernel (no shared-memory staging) everywhere.
+ * Returns the old value. */
 int pa_decode_force_path(int path);
 /* Split-K granularity of the fast path (guided self-scheduling): a unit handed out when
  * `remaining` blocks are left is about remaining / (guided_k * SMs) blocks (default 3), never

@@ -38,9 +38,10 @@ def lib():
     return _lib.load()
 
 
-@pytest.fixture()
-def force_generic(lib):
-    old = lib.pa_decode_force_path(1)
+@pytest.fixture(params=[1, 2], ids=["stream", "plain"])
+def force_generic(lib, request):
+    """1 = no TMA kernel (the cp.async streaming kernel where rows are 16-byte aligned), 2 = the plain generic kernel."""
+    old = lib.pa_decode_force_path(request.param)
     yield
     lib.pa_decode_force_path(old)
 
@@ -219,11 +220,11 @@ RAGGED = [
 
 
 @pytest.mark.parametrize("cfg", RAGGED, ids=lambda c: f"hq{c[0]}kv{c[1]}d{c[2]}bs{c[3]}{'bf16' if c[4] == torch.bfloat16 else 'f32'}")
-@pytest.mark.parametrize("path", ["auto", "generic"])
+@pytest.mark.parametrize("path", ["auto", "generic", "plain"])
 def test_decode_batched_ragged_vs_oracle(P, lib, cfg, path):
     hq, hkv, d, bs, dtype, lens = cfg
     q, kv, bts, bts_safe, sl = _make_batch(len(lens), hq, hkv, d, bs, lens, dtype, seed=len(lens) * 7 + d)
-    old = lib.pa_decode_force_path(1 if path == "generic" else 0)
+    old = lib.pa_decode_force_path({"auto": 0, "generic": 1, "plain": 2}[path])
     try:
         out = P.paged_attention_decode_batched(q.to(DEV), kv.to(DEV), bts.to(DEV), sl.to(DEV))
     finally:
@@ -415,13 +416,14 @@ def test_garbage_past_seq_len_is_ignored(P):
     assert torch.equal(ref, got)
     old = os.environ.get("X")
     from vllm_from_scratch_b200 import _lib
-    prev = _lib.load().pa_decode_force_path(1)
-    try:
-        got_g = P.paged_attention_decode_batched(q, kv2, bts.to(DEV), lens.to(DEV))
-    finally:
-        _lib.load().pa_decode_force_path(prev)
-    assert not torch.isnan(got_g).any()
-    assert (got_g.float() - ref.float()).abs().max().item() <= 2e-2
+    for path in (1, 2):
+        prev = _lib.load().pa_decode_force_path(path)
+        try:
+            got_g = P.paged_attention_decode_batched(q, kv2, bts.to(DEV), lens.to(DEV))
+        finally:
+            _lib.load().pa_decode_force_path(prev)
+        assert not torch.isnan(got_g).any()
+        assert (got_g.float() - ref.float()).abs().max().item() <= 2e-2
 
 
 # =========================================================================================

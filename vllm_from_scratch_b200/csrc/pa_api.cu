@@ -196,10 +196,11 @@ static int decode_impl(const void* q, int64_t q_stride_b, int64_t q_stride_h, vo
   p.pos_head = 0;
   p.scale_log2e = (float)((1.0 / sqrt((double)D)) * 1.4426950408889634);
 
-  const bool tma = g_force_path.load() != 1 && pa_decode_tma_supported(p, cache->dtype) &&
+  const bool tma = g_force_path.load() == 0 && pa_decode_tma_supported(p, cache->dtype) &&
                    tma_header_fits(batch, Hkv);
   if (peers && !tma) return PA_ERR_UNSUPPORTED;          // the fused gather lives in the fast-path kernel only
   int ctas = 0;
+  bool stream_path = false;
   int64_t slots;
   int rows;
   p.num_stages = g_stages.load();
@@ -216,7 +217,9 @@ static int decode_impl(const void* q, int64_t q_stride_b, int64_t q_stride_h, vo
   } else {
     p.tile_q = 8;
     p.q_tiles = (p.group + 7) / 8;
-    p.num_workers = pa_decode_generic_workers(sms, &ctas);
+    // 16-byte aligned rows: the cp.async streaming kernel; anything else: the plain generic kernel
+    stream_path = g_force_path.load() != 2 && pa_decode_stream_supported(p, cache->dtype);
+    p.num_workers = stream_path ? pa_decode_stream_workers(sms, &ctas) : pa_decode_generic_workers(sms, &ctas);
     slots = (int64_t)batch * Hkv * p.q_tiles + p.num_workers;
     rows = p.tile_q;
   }
@@ -236,7 +239,9 @@ static int decode_impl(const void* q, int64_t q_stride_b, int64_t q_stride_h, vo
     if (g_prof.on && g_prof.used < g_prof.cap) pe = &g_prof.ev[3 * g_prof.used++];
   }
   if (pe) cudaEventRecord(pe[0], st);
-  int rc = tma ? pa_launch_decode_tma(p, sms, st) : pa_launch_decode_generic(p, cache->dtype, ctas, st);
+  int rc = tma ? pa_launch_decode_tma(p, sms, st)
+               : stream_path ? pa_launch_decode_stream(p, cache->dtype, ctas, st)
+                             : pa_launch_decode_generic(p, cache->dtype, ctas, st);
   if (rc) return rc;
   if (pe) cudaEventRecord(pe[1], st);
   if (!tma) rc = pa_launch_reduce(p, cache->dtype, st);      // the TMA kernel merges its own partials
