@@ -427,8 +427,8 @@ def c5_point(torch, P, dev, world, rank, steps, timer):
 
 
 def generic_f32_point(torch, P, dev, steps, timer, peak):
-    """The generic kernel (fp32 KV cache = the reference's default dtype, and every odd shape) on the C2 batch:
-    KV bytes double.  Two launches per step (split-K + reduce)."""
+    """The generic streaming kernel (fp32 KV cache = the reference's default dtype, and every odd shape with
+    16-byte aligned rows) on the C2 batch: KV bytes double.  Two launches per step (split-K + reduce)."""
     b, ctx, hq, hkv, d, bs, _, _ = WORKLOADS["c2"]
     layers = 2
     nblk = ctx // bs
@@ -456,7 +456,7 @@ def generic_f32_point(torch, P, dev, steps, timer, peak):
     del pool, caches, graphs
     torch.cuda.empty_cache()
     return {"workload": "C2 batch with an fp32 KV cache (64 x 2048, 32/8 heads, head_dim 128): generic kernel",
-            "kernel": "pa_decode_generic_kernel<float> + pa_reduce_kernel<float>", "launches_per_step": 2, "steps": n,
+            "kernel": "pa_decode_stream_kernel<float> (cp.async-staged) + pa_reduce_kernel<float>", "launches_per_step": 2, "steps": n,
             "ms_per_step": ms / n, "tokens_per_s": b / (ms / n * 1e-3), "algorithmic_bytes_per_step": kv_bytes + io_bytes,
             "achieved_gbs": ach, "peak_gbs": peak, "frac": ach / peak, "frac_of_nominal_8tbs": ach / NOMINAL_HBM_GBS}
 

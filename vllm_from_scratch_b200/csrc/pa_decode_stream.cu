@@ -85,7 +85,9 @@ __device__ __forceinline__ void cp_wait(int pending) {     // at most `pending` 
 }
 
 // T: cache / q / out element type.  CPL: 16-byte chunks of a V row per lane (head_dim <= 32 * CPL * N).
-template <typename T, int CPL>
+// GQ: query heads computed per head segment (4 when the GQA group is <= 4, else the full tile of 8): the
+// kernel is bound by instruction issue at 8 warps per SM, so nothing is spent on predicated-off heads.
+template <typename T, int CPL, int GQ>
 __global__ void __launch_bounds__(kWarpsS * 32, 1)
 pa_decode_stream_kernel(const PaDecodeParams p) {
   constexpr int N = Chunk<T>::N;
@@ -126,6 +128,7 @@ pa_decode_stream_kernel(const PaDecodeParams p) {
   const uint32_t my_q_s = static_cast<uint32_t>(__cvta_generic_to_shared(my_q));
   const int g = p.group;
   const int tg = lane >> 3, q8 = lane & 7;              // QK^T: token of the group of 4, eighth of the row
+  const int r_first = lane / cpr, c_first = lane % cpr, r_step = 32 / cpr, c_step = 32 % cpr;   // cp.async chunk walk
 
   PaCursor cc = pa_locate(s_cum, p.batch, hs, lin0);
   int done = 0;
@@ -142,136 +145,130 @@ pa_decode_stream_kernel(const PaDecodeParams p) {
     const int64_t head_off = (int64_t)kvh * p.kv_stride_head;
 
     __syncwarp();
-    for (int i = lane; i < kTQ * D; i += 32) {
+    for (int i = lane; i < GQ * D; i += 32) {            // rows past the live heads are zeros: their scores stay 0
       const int j = i / D, d = i - j * D;
       my_q[i] = j < gq ? pa_to_float(qbase[(int64_t)cc.s * p.q_stride_b + (int64_t)(hq0 + j) * p.q_stride_h + d]) : 0.f;
     }
     __syncwarp();
 
-    float m_run[kTQ], l_run[kTQ], acc[kTQ][CPL * N];
+    float m_run[GQ], l_run[GQ], acc[GQ][CPL * N];
 #pragma unroll
-    for (int j = 0; j < kTQ; ++j) {
+    for (int j = 0; j < GQ; ++j) {
       m_run[j] = -INFINITY;
       l_run[j] = 0.f;
 #pragma unroll
       for (int i = 0; i < CPL * N; ++i) acc[j][i] = 0.f;
     }
 
-    // stage = a run of <= TS consecutive tokens inside one block: K rows, then V rows
-    auto stage_len = [&](int t) { return min(min(TS, BS - t % BS), tok_end - t); };
-    auto issue = [&](int t, int n, int st) {
-      const int blk = t / BS;
-      const int64_t base = (int64_t)__ldg(bt + blk) * p.kv_stride_block + head_off + (int64_t)(t - blk * BS) * p.kv_stride_slot;
+    // stage = a run of <= TS consecutive tokens inside one block: K rows, then V rows.  The producer cursor
+    // (pt: token, pblk / poff: its block and offset in the block) and the consumer cursor advance by the same rule.
+    auto issue = [&](int blk, int off, int n, int st) {
+      const int64_t base = (int64_t)__ldg(bt + blk) * p.kv_stride_block + head_off + (int64_t)off * p.kv_stride_slot;
       const uint32_t dst0 = my_ring + (uint32_t)st * L.stage_bytes;
-      const int nchunks = 2 * n * cpr;
-      for (int i = lane; i < nchunks; i += 32) {
-        const int r = i / cpr, c = i - r * cpr;
+      // chunk i = lane, lane + 32, ... of the 2 n rows (K rows then V rows), cpr chunks per row: (row, chunk) advance
+      // without a division
+      int r = r_first, c = c_first;
+      while (r < 2 * n) {
         const bool is_v = r >= n;
         const int tt = is_v ? r - n : r;
         const T* src = (is_v ? vbase : kbase) + base + (int64_t)tt * p.kv_stride_slot + c * N;
         cp_async16(dst0 + (uint32_t)((is_v ? TS + tt : tt) * row_bytes + c * 16), src);
+        r += r_step;
+        c += c_step;
+        if (c >= cpr) { c -= cpr; ++r; }
       }
     };
 
-    int pt = cc.b * BS, ct = pt, ps = 0, cs = 0;
-    for (int i = 0; i < R - 1; ++i) {
+    int pt = cc.b * BS, pblk = cc.b, poff = 0, ct = pt, coff = 0, ps = 0, cs = 0;
+    auto produce = [&]() {
       if (pt < tok_end) {
-        const int n = stage_len(pt);
-        issue(pt, n, ps);
+        const int n = min(min(TS, BS - poff), tok_end - pt);
+        issue(pblk, poff, n, ps);
         pt += n;
+        poff += n;
+        if (poff == BS) { poff = 0; ++pblk; }
         ps = ps + 1 == R ? 0 : ps + 1;
       }
       cp_commit();
-    }
+    };
+    for (int i = 0; i < R - 1; ++i) produce();
     while (ct < tok_end) {
-      if (pt < tok_end) {
-        const int n = stage_len(pt);
-        issue(pt, n, ps);
-        pt += n;
-        ps = ps + 1 == R ? 0 : ps + 1;
-      }
-      cp_commit();
+      produce();
       cp_wait(R - 1);
       __syncwarp();
-      const int n = stage_len(ct);
+      const int n = min(min(TS, BS - coff), tok_end - ct);
       const uint32_t kst = my_ring + (uint32_t)cs * L.stage_bytes;
       const uint32_t vst = kst + (uint32_t)TS * row_bytes;
 
-      // ---- scores of the stage's tokens: group gi holds tokens 4 gi .. 4 gi + 3 ------------------
-      float sc[2][kTQ];
+      // ---- scores of the stage's tokens: lane's tokens tg (group 0) and 4 + tg (group 1) ------------
+      float sc[2][GQ];
 #pragma unroll
-      for (int gi = 0; gi < 2; ++gi) {
+      for (int j = 0; j < GQ; ++j) sc[0][j] = sc[1][j] = 0.f;
+      const bool v0 = tg < n, v1 = 4 + tg < n;
+      for (int c = q8; c < cpr; c += 8) {
+        float k0[N], k1[N];
 #pragma unroll
-        for (int j = 0; j < kTQ; ++j) sc[gi][j] = 0.f;
-        const int ti = gi * 4 + tg;
-        if (gi * 4 < n && ti < n) {
-          for (int c = q8; c < cpr; c += 8) {
-            float kf[N];
-            Chunk<T>::load(kst + (uint32_t)(ti * row_bytes + c * 16), kf);
+        for (int e = 0; e < N; ++e) k0[e] = k1[e] = 0.f;
+        if (v0) Chunk<T>::load(kst + (uint32_t)(tg * row_bytes + c * 16), k0);
+        if (v1) Chunk<T>::load(kst + (uint32_t)((4 + tg) * row_bytes + c * 16), k1);
 #pragma unroll
-            for (int j = 0; j < kTQ; ++j) {
-              if (j < gq) {
+        for (int j = 0; j < GQ; ++j) {
 #pragma unroll
-                for (int e = 0; e < N; e += 4) {
-                  float qv[4];
-                  Chunk<float>::load(my_q_s + (uint32_t)((j * D + c * N + e) * 4), qv);
-                  sc[gi][j] = fmaf(kf[e], qv[0], sc[gi][j]);
-                  sc[gi][j] = fmaf(kf[e + 1], qv[1], sc[gi][j]);
-                  sc[gi][j] = fmaf(kf[e + 2], qv[2], sc[gi][j]);
-                  sc[gi][j] = fmaf(kf[e + 3], qv[3], sc[gi][j]);
-                }
-              }
+          for (int e = 0; e < N; e += 4) {
+            float qv[4];
+            Chunk<float>::load(my_q_s + (uint32_t)((j * D + c * N + e) * 4), qv);
+#pragma unroll
+            for (int x = 0; x < 4; ++x) {
+              sc[0][j] = fmaf(k0[e + x], qv[x], sc[0][j]);
+              sc[1][j] = fmaf(k1[e + x], qv[x], sc[1][j]);
             }
           }
         }
-        if (gi * 4 < n) {
+      }
 #pragma unroll
-          for (int j = 0; j < kTQ; ++j) {
-            if (j < gq) {
-              float v = sc[gi][j];
-              v += __shfl_xor_sync(0xffffffffu, v, 1);
-              v += __shfl_xor_sync(0xffffffffu, v, 2);
-              v += __shfl_xor_sync(0xffffffffu, v, 4);
-              sc[gi][j] = v;
-            }
-          }
+      for (int gi = 0; gi < 2; ++gi) {
+#pragma unroll
+        for (int j = 0; j < GQ; ++j) {
+          float v = sc[gi][j];
+          v += __shfl_xor_sync(0xffffffffu, v, 1);
+          v += __shfl_xor_sync(0xffffffffu, v, 2);
+          v += __shfl_xor_sync(0xffffffffu, v, 4);
+          sc[gi][j] = v;
         }
       }
       // ---- online softmax over the stage -------------------------------------------------------
 #pragma unroll
-      for (int j = 0; j < kTQ; ++j) {
-        if (j < gq) {
-          const float s0 = tg < n ? sc[0][j] * p.scale_log2e : -INFINITY;
-          const float s1 = 4 + tg < n ? sc[1][j] * p.scale_log2e : -INFINITY;
-          float mx = fmaxf(s0, s1);
-          mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
-          mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
-          const float m_new = fmaxf(m_run[j], mx);       // finite: the stage's first token is valid
-          const float alpha = exp2f(m_run[j] - m_new);
-          m_run[j] = m_new;
-          const float p0 = exp2f(s0 - m_new), p1 = exp2f(s1 - m_new);
-          float ps_ = p0 + p1;                             // every lane of a token's group holds the same value
-          ps_ += __shfl_xor_sync(0xffffffffu, ps_, 8);
-          ps_ += __shfl_xor_sync(0xffffffffu, ps_, 16);
-          l_run[j] = l_run[j] * alpha + ps_;
+      for (int j = 0; j < GQ; ++j) {
+        const float s0 = v0 ? sc[0][j] * p.scale_log2e : -INFINITY;
+        const float s1 = v1 ? sc[1][j] * p.scale_log2e : -INFINITY;
+        float mx = fmaxf(s0, s1);
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+        const float m_new = fmaxf(m_run[j], mx);         // finite: the stage's first token is valid
+        const float alpha = exp2f(m_run[j] - m_new);
+        m_run[j] = m_new;
+        const float p0 = exp2f(s0 - m_new), p1 = exp2f(s1 - m_new);
+        float ps_ = p0 + p1;                               // every lane of a token's group holds the same value
+        ps_ += __shfl_xor_sync(0xffffffffu, ps_, 8);
+        ps_ += __shfl_xor_sync(0xffffffffu, ps_, 16);
+        l_run[j] = l_run[j] * alpha + ps_;
 #pragma unroll
-          for (int i = 0; i < CPL * N; ++i) acc[j][i] *= alpha;
-          if (q8 == 0) {
-            my_w[tg * kTQ + j] = p0;
-            my_w[(4 + tg) * kTQ + j] = p1;
-          }
+        for (int i = 0; i < CPL * N; ++i) acc[j][i] *= alpha;
+        if (q8 == 0) {
+          my_w[tg * GQ + j] = p0;
+          my_w[(4 + tg) * GQ + j] = p1;
         }
       }
       __syncwarp();
       // ---- PV: lane <-> 16-byte column chunk ---------------------------------------------------
       for (int t = 0; t < n; ++t) {
-        float w[kTQ];
-        {
-          float w0[4], w1[4];
-          Chunk<float>::load(my_w_s + (uint32_t)(t * kTQ * 4), w0);
-          Chunk<float>::load(my_w_s + (uint32_t)(t * kTQ * 4 + 16), w1);
+        float w[GQ];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) { w[j] = w0[j]; w[4 + j] = w1[j]; }
+        for (int j0 = 0; j0 < GQ; j0 += 4) {
+          float w4[4];
+          Chunk<float>::load(my_w_s + (uint32_t)((t * GQ + j0) * 4), w4);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) w[j0 + j] = w4[j];
         }
 #pragma unroll
         for (int ci = 0; ci < CPL; ++ci) {
@@ -280,17 +277,17 @@ pa_decode_stream_kernel(const PaDecodeParams p) {
             float vf[N];
             Chunk<T>::load(vst + (uint32_t)(t * row_bytes + c * 16), vf);
 #pragma unroll
-            for (int j = 0; j < kTQ; ++j) {
-              if (j < gq) {
+            for (int j = 0; j < GQ; ++j) {
 #pragma unroll
-                for (int e = 0; e < N; ++e) acc[j][ci * N + e] = fmaf(w[j], vf[e], acc[j][ci * N + e]);
-              }
+              for (int e = 0; e < N; ++e) acc[j][ci * N + e] = fmaf(w[j], vf[e], acc[j][ci * N + e]);
             }
           }
         }
       }
       __syncwarp();                                      // the stage (and the weight tile) may be overwritten
       ct += n;
+      coff += n;
+      if (coff == BS) coff = 0;
       cs = cs + 1 == R ? 0 : cs + 1;
     }
     cp_wait(0);
@@ -300,7 +297,7 @@ pa_decode_stream_kernel(const PaDecodeParams p) {
     const bool whole = (seg_lin0 / per) == ((seg_lin0 + cc.n - 1) / per);
     const int slot = cc.s * hs + cc.h + worker;
 #pragma unroll
-    for (int j = 0; j < kTQ; ++j) {
+    for (int j = 0; j < GQ; ++j) {
       if (j < gq) {
         const float l = l_run[j];
         if (whole) {
@@ -336,10 +333,10 @@ pa_decode_stream_kernel(const PaDecodeParams p) {
   }
 }
 
-template <typename T, int CPL>
+template <typename T, int CPL, int GQ>
 int launch_s(const PaDecodeParams& p, int ctas, cudaStream_t stream) {
   const StreamLayout L = stream_layout(p.head_dim, (int)sizeof(T), p.batch);
-  auto kern = pa_decode_stream_kernel<T, CPL>;
+  auto kern = pa_decode_stream_kernel<T, CPL, GQ>;
   static PaPerDeviceFlag attr;
   const int dev = attr.need();
   if (dev != -2) {
@@ -371,6 +368,11 @@ bool pa_decode_stream_supported(const PaDecodeParams& p, int dtype) {
 int pa_launch_decode_stream(const PaDecodeParams& p, int dtype, int ctas, cudaStream_t stream) {
   const int esize = dtype == 1 ? 4 : 2;
   const int cpr = p.head_dim * esize / 16;
-  if (dtype == 1) return cpr <= 32 ? launch_s<float, 1>(p, ctas, stream) : launch_s<float, 2>(p, ctas, stream);
-  return cpr <= 32 ? launch_s<__nv_bfloat16, 1>(p, ctas, stream) : launch_s<__nv_bfloat16, 2>(p, ctas, stream);
+  const bool g4 = p.group <= 4;               // every head segment has <= 4 live query heads
+  if (dtype == 1) {
+    if (cpr <= 32) return g4 ? launch_s<float, 1, 4>(p, ctas, stream) : launch_s<float, 1, 8>(p, ctas, stream);
+    return g4 ? launch_s<float, 2, 4>(p, ctas, stream) : launch_s<float, 2, 8>(p, ctas, stream);
+  }
+  if (cpr <= 32) return g4 ? launch_s<__nv_bfloat16, 1, 4>(p, ctas, stream) : launch_s<__nv_bfloat16, 1, 8>(p, ctas, stream);
+  return g4 ? launch_s<__nv_bfloat16, 2, 4>(p, ctas, stream) : launch_s<__nv_bfloat16, 2, 8>(p, ctas, stream);
 }
