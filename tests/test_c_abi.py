@@ -70,3 +70,25 @@ def test_status_strings_and_argument_validation_without_a_gpu(lib):
     assert lib.pa_decode_gather(None, 0, 0, None, 0, 0, None, None, 0, None, 1, 1, None, 0, None, None) < 0
     # empty work is a no-op success
     assert lib.pa_copy_blocks(None, 0, 0, 0, 0, None, 0, None) == 0
+
+
+def test_torch_shim_loads_and_mirrors_the_error_contract():
+    """The thin torch C++ extension (csrc/torch_shim.cpp) is built in-tree, reports the same ABI version and raises
+    the host mirror's exception types without touching a device (CPU tensors: RuntimeError, no CPU fallback)."""
+    import pytest
+    import torch
+    from vllm_from_scratch_b200 import _lib, paged_attention as P
+    ext = _lib.load_ext()
+    assert ext.abi_version() == _lib.ABI_VERSION
+    for name in ("reshape_and_cache", "rope_and_cache", "decode", "prefill_varlen", "prefill_chunk", "block_table_step",
+                 "prefill_tc_available", "decode_workspace_bytes"):
+        assert callable(getattr(ext, name))
+    assert ext.decode_workspace_bytes(64, 32, 8, 128) == _lib.load().pa_decode_workspace_bytes(64, 32, 8, 128)
+    k = torch.zeros(4, 16, 2, 8)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        P.reshape_and_cache(torch.zeros(3, 2, 8), torch.zeros(3, 2, 8), (k, k.clone()), torch.arange(3))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        P.paged_attention_decode_batched(torch.zeros(1, 2, 8), (k, k.clone()), torch.zeros(1, 1, dtype=torch.int32),
+                                         torch.ones(1, dtype=torch.int32), workspace=torch.zeros(8))
+    with pytest.raises(TypeError):
+        P.reshape_and_cache("not a tensor", torch.zeros(3, 2, 8), (k, k.clone()), torch.arange(3))

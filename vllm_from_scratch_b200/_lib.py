@@ -121,6 +121,28 @@ def load() -> ctypes.CDLL:
     return lib
 
 
+_ext = None
+
+
+def load_ext():
+    """The thin torch C++ extension over the same C ABI (csrc/torch_shim.cpp -> _pa_torch.so): tensors in, one
+    extern "C" call out.  The hot per-layer entry points go through it (3 us of host time instead of ~20 us through
+    ctypes); setup, peer plumbing, block copy / swap and the debug hooks stay on ctypes.  Fails loudly when missing."""
+    global _ext
+    if _ext is not None:
+        return _ext
+    load()
+    try:
+        from . import _pa_torch
+    except ImportError as e:
+        raise RuntimeError(f"vllm_from_scratch_b200/_pa_torch.so is missing or does not load ({e}): build it with "
+                           "`python -m vllm_from_scratch_b200.build`.  There is no fallback binding.") from e
+    if _pa_torch.abi_version() != ABI_VERSION:
+        raise RuntimeError(f"_pa_torch.so was built against ABI {_pa_torch.abi_version()} != {ABI_VERSION}: rebuild it")
+    _ext = _pa_torch
+    return _ext
+
+
 def check(rc: int, what: str) -> None:
     if rc != 0:
         msg = load().pa_status_string(rc).decode()

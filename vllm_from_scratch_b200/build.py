@@ -77,5 +77,40 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+# ---- the thin torch C++ extension (csrc/torch_shim.cpp) -----------------------------------------------
+SHIM_SRC = os.path.join(CSRC, "torch_shim.cpp")
+SHIM = os.path.join(HERE, "_pa_torch.so")
+
+
+def build_torch_shim(force: bool = False) -> str:
+    """Compile csrc/torch_shim.cpp in-tree against this interpreter's torch (g++ only: the shim holds no device
+    code) and link it to libpa_b200.so through an $ORIGIN rpath.  Torch is needed HERE, not in libpa_b200.so."""
+    build_library()
+    if not force and not _stale(SHIM, [SHIM_SRC, os.path.join(INCLUDE, "pa_b200.h"), LIB]):
+        return SHIM
+    import sysconfig
+
+    import torch
+    from torch.utils import cpp_extension as ce
+    cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
+    inc = []
+    for d in ce.include_paths("cuda") + [sysconfig.get_paths()["include"]]:
+        inc += ["-isystem", d]
+    libdirs = ce.library_paths("cuda")
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-DTORCH_EXTENSION_NAME=_pa_torch", "-DTORCH_API_INCLUDE_EXTENSION_H",
+           f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}", "-Wno-attributes"] + inc + [SHIM_SRC, "-o", SHIM]
+    for d in libdirs:
+        cmd += ["-L", d, f"-Wl,-rpath,{d}"]
+    cmd += ["-L", HERE, "-l:libpa_b200.so", "-Wl,-rpath,$ORIGIN", "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch_cuda", "-ltorch",
+            "-ltorch_python"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    with open(os.path.join(BUILD, "torch_shim.log"), "w") as f:
+        f.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
+    if r.returncode != 0:
+        raise RuntimeError("torch shim build failed:\n" + (r.stdout + r.stderr)[-4000:])
+    return SHIM
+
+
 if __name__ == "__main__":
     print(build_library(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    print(build_torch_shim(force="--force" in sys.argv))

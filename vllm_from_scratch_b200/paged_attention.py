@@ -102,6 +102,13 @@ def _describe_cache(kv_cache: KvCacheArg) -> Tuple[PaKvCache, torch.Tensor]:
     return desc, k
 
 
+def _split_cache(kv_cache: KvCacheArg):
+    """(k_cache, v_cache) pair -> the two tensors; a single [2, NB, Hkv, BS, D] tensor -> (tensor, None)."""
+    if isinstance(kv_cache, (tuple, list)):
+        return kv_cache[0], kv_cache[1]
+    return kv_cache, None
+
+
 _workspaces = {}
 
 
@@ -229,34 +236,7 @@ def block_table_step(table: torch.Tensor, updates: Optional[torch.Tensor], num_u
     of which the first ``num_updates[0]`` (a DEVICE int32) are applied; then
     ``step_table[j, :n] = table[row_of[j], :n]`` with ``n = ceil(ctx_lens[j] / block_size)`` for every
     ``j < len(row_of)`` (``row_of[j] < 0`` leaves row j alone).  No host sync; graph-capturable."""
-    _require_cuda(table, "table")
-    if table.dtype != torch.int32 or table.dim() != 2 or table.stride(1) != 1:
-        raise ValueError("table must be int32 [rows, W] with a contiguous last axis")
-    max_upd = 0
-    upd_ptr = nupd_ptr = row_ptr = len_ptr = st_ptr = 0
-    if updates is not None and updates.numel():
-        _require_cuda(updates, "updates")
-        _require_cuda(num_updates, "num_updates")
-        if updates.dtype != torch.int32 or num_updates.dtype != torch.int32 or not updates.is_contiguous():
-            raise ValueError("updates must be contiguous int32 [cap, 3] and num_updates an int32 device tensor")
-        max_upd = updates.numel() // 3
-        upd_ptr, nupd_ptr = updates.data_ptr(), num_updates.data_ptr()
-    n_gather, st_stride = 0, 0
-    if row_of is not None and row_of.numel():
-        for name, ten in (("row_of", row_of), ("ctx_lens", ctx_lens), ("step_table", step_table)):
-            _require_cuda(ten, name)
-            if ten.dtype != torch.int32:
-                raise ValueError(f"{name} must be int32")
-        n_gather = row_of.numel()
-        if ctx_lens.numel() != n_gather or step_table.dim() != 2 or step_table.shape[0] < n_gather \
-                or step_table.stride(1) != 1 or not row_of.is_contiguous() or not ctx_lens.is_contiguous():
-            raise ValueError("row_of / ctx_lens must be contiguous [n] and step_table [>= n, W]")
-        row_ptr, len_ptr, st_ptr, st_stride = row_of.data_ptr(), ctx_lens.data_ptr(), step_table.data_ptr(), step_table.stride(0)
-    with _DeviceOf(table):
-        rc = _lib.load().pa_block_table_step(table.data_ptr(), table.stride(0), table.shape[0], upd_ptr, nupd_ptr,
-                                             max_upd, row_ptr, len_ptr, n_gather, block_size, st_ptr, st_stride,
-                                             _stream_ptr())
-    _lib.check(rc, "pa_block_table_step")
+    _lib.load_ext().block_table_step(table, updates, num_updates, row_of, ctx_lens, step_table, int(block_size))
 
 
 # ---------------------------------------------------------------------------------------
@@ -267,29 +247,8 @@ def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, kv_cache: KvCacheA
     """Scatter new K/V rows ``[T, Hkv, D]`` into the paged cache by slot (slot = block * BS +
     offset; negative = skip).  Bit-exact copy.  Replaces paged_attention.py:48-51, :119-123
     and mini_vllm.py:424-427."""
-    desc, kplane = _describe_cache(kv_cache)
-    _require_cuda(key, "key")
-    _require_cuda(value, "value")
-    _require_cuda(slot_mapping, "slot_mapping")
-    if key.dim() != 3 or key.shape != value.shape:
-        raise ValueError("key / value must both be [T, Hkv, D]")
-    t, h, d = key.shape
-    if h != desc.num_kv_heads or d != desc.head_dim:
-        raise ValueError(f"key is [T, {h}, {d}] but the cache holds {desc.num_kv_heads} heads of dim {desc.head_dim}")
-    if key.dtype != kplane.dtype or value.dtype != kplane.dtype:
-        raise TypeError(f"key/value dtype {key.dtype}/{value.dtype} != cache dtype {kplane.dtype}")
-    if slot_mapping.numel() != t:
-        raise ValueError("slot_mapping must have one entry per token")
-    if key.stride(2) != 1 and d > 1:
-        key = key.contiguous()
-    if value.stride() != key.stride():
-        value = value.contiguous()
-        key = key.contiguous()
-    slots = slot_mapping.to(torch.int64).contiguous()
-    with _DeviceOf(kplane):
-        rc = _lib.load().pa_reshape_and_cache(key.data_ptr(), value.data_ptr(), key.stride(0), key.stride(1),
-                                              ctypes.byref(desc), slots.data_ptr(), t, _stream_ptr())
-    _lib.check(rc, "pa_reshape_and_cache")
+    ca, cb = _split_cache(kv_cache)
+    _lib.load_ext().reshape_and_cache(key, value, ca, cb, slot_mapping)
 
 
 def rope_and_cache(qkv: torch.Tensor, positions: torch.Tensor, cos_cached: torch.Tensor, sin_cached: torch.Tensor,
@@ -301,34 +260,8 @@ def rope_and_cache(qkv: torch.Tensor, positions: torch.Tensor, cos_cached: torch
     ``[max_len, D]`` are the reference ``RotaryEmbedding``'s own buffers.  Returns rotated Q
     ``[T, Hq, D]``; rotated K and plain V land in their cache slots.  Bit-exact against the
     reference's op-by-op torch evaluation in the same dtype."""
-    desc, kplane = _describe_cache(kv_cache)
-    for name, ten in (("qkv", qkv), ("positions", positions), ("cos_cached", cos_cached), ("sin_cached", sin_cached),
-                      ("slot_mapping", slot_mapping)):
-        _require_cuda(ten, name)
-    d, hkv = desc.head_dim, desc.num_kv_heads
-    if qkv.dim() != 2 or qkv.shape[1] != (num_q_heads + 2 * hkv) * d:
-        raise ValueError(f"qkv must be [T, {(num_q_heads + 2 * hkv) * d}]")
-    if not (qkv.dtype == cos_cached.dtype == sin_cached.dtype == kplane.dtype):
-        raise TypeError("qkv, the cos / sin tables and the cache must share one dtype")
-    if cos_cached.shape != sin_cached.shape or cos_cached.dim() != 2 or cos_cached.shape[1] != d:
-        raise ValueError("cos_cached / sin_cached must be [max_len, D]")
-    t = qkv.shape[0]
-    if positions.numel() != t or slot_mapping.numel() != t:
-        raise ValueError("positions and slot_mapping must have one entry per token")
-    if qkv.stride(1) != 1:
-        qkv = qkv.contiguous()
-    cos_cached, sin_cached = cos_cached.contiguous(), sin_cached.contiguous()
-    if q_out is None:
-        q_out = torch.empty((t, num_q_heads, d), dtype=qkv.dtype, device=qkv.device)
-    pos = positions.to(torch.int64).contiguous()
-    slots = slot_mapping.to(torch.int64).contiguous()
-    with _DeviceOf(kplane):
-        rc = _lib.load().pa_rope_and_cache(qkv.data_ptr(), qkv.stride(0), num_q_heads, cos_cached.data_ptr(),
-                                           sin_cached.data_ptr(), cos_cached.stride(0), cos_cached.shape[0],
-                                           pos.data_ptr(), slots.data_ptr(), t, q_out.data_ptr(), q_out.stride(0),
-                                           q_out.stride(1), ctypes.byref(desc), _stream_ptr())
-    _lib.check(rc, "pa_rope_and_cache")
-    return q_out
+    ca, cb = _split_cache(kv_cache)
+    return _lib.load_ext().rope_and_cache(qkv, positions, cos_cached, sin_cached, ca, cb, slot_mapping, int(num_q_heads), q_out)
 
 
 # ---------------------------------------------------------------------------------------
@@ -354,55 +287,15 @@ def paged_attention_decode_batched(query: torch.Tensor, kv_cache: KvCacheArg, bl
     counter header).  ``peers`` (a ``_lib.PaPeerGather``, built by ``sharding.PeerGather``) fuses the
     KV-head-sharded output gather into the kernel: rows are also stored into the remote ranks'
     gather buffers over NVLink and arrival counters are bumped (``pa_decode_gather``)."""
-    desc, kplane = _describe_cache(kv_cache)
-    _require_cuda_or_pinned(query, "query")
-    _require_cuda(block_tables, "block_tables")
-    _require_cuda(seq_lens, "seq_lens")
-    if query.dim() != 3:
-        raise ValueError("query must be [B, Hq, D]")
-    b, hq, d = query.shape
-    if d != desc.head_dim:
-        raise ValueError(f"query head_dim {d} != cache head_dim {desc.head_dim}")
-    if hq % desc.num_kv_heads:
-        raise ValueError(f"num_q_heads {hq} is not a multiple of num_kv_heads {desc.num_kv_heads}")
-    if query.dtype != kplane.dtype:
-        raise TypeError(f"query dtype {query.dtype} != cache dtype {kplane.dtype}")
-    if block_tables.dtype != torch.int32 or seq_lens.dtype != torch.int32:
-        raise TypeError("block_tables and seq_lens must be int32 device tensors")
-    if block_tables.dim() != 2 or block_tables.shape[0] != b or seq_lens.numel() != b:
-        raise ValueError("block_tables must be [B, max_blocks] and seq_lens [B]")
-    if block_tables.shape[1] > 1 and block_tables.stride(1) != 1:
-        block_tables = block_tables.contiguous()
-    if query.stride(2) != 1 and d > 1:
-        query = query.contiguous()
-    seq_lens = seq_lens.contiguous()
-    if out is None:
-        out = torch.empty((b, hq, d), dtype=query.dtype, device=kplane.device)
-    else:
-        _require_cuda_or_pinned(out, "out")
-        if out.shape != (b, hq, d) or out.dtype != query.dtype or (out.stride(2) != 1 and d > 1):
-            raise ValueError("out must be [B, Hq, D] with the query's dtype and a contiguous last axis")
-    lib = _lib.load()
-    need = lib.pa_decode_workspace_bytes(b, hq, desc.num_kv_heads, d)
+    ca, cb = _split_cache(kv_cache)
+    ext = _lib.load_ext()
     if workspace is None:
-        workspace = _workspace(kplane.device, need)
-    elif not workspace.is_cuda or workspace.numel() * workspace.element_size() < need:
-        raise ValueError(f"workspace must be a CUDA tensor of at least {need} bytes")
-    with _DeviceOf(kplane):
-        if peers is None:
-            rc = lib.pa_decode(query.data_ptr(), query.stride(0), query.stride(1),
-                               out.data_ptr(), out.stride(0), out.stride(1),
-                               ctypes.byref(desc), block_tables.data_ptr(), block_tables.stride(0),
-                               seq_lens.data_ptr(), b, hq, workspace.data_ptr(),
-                               workspace.numel() * workspace.element_size(), _stream_ptr())
-        else:
-            rc = lib.pa_decode_gather(query.data_ptr(), query.stride(0), query.stride(1),
-                                      out.data_ptr(), out.stride(0), out.stride(1),
-                                      ctypes.byref(desc), block_tables.data_ptr(), block_tables.stride(0),
-                                      seq_lens.data_ptr(), b, hq, workspace.data_ptr(),
-                                      workspace.numel() * workspace.element_size(), ctypes.byref(peers), _stream_ptr())
-    _lib.check(rc, "pa_decode" if peers is None else "pa_decode_gather")
-    return out
+        # both layouts keep the KV heads on axis 2 ([2, NB, Hkv, BS, D] and [NB, BS, H, D]); malformed arguments
+        # are reported by the extension's own checks
+        need = ext.decode_workspace_bytes(query.shape[0], query.shape[1], ca.shape[2], query.shape[-1]) \
+            if query.dim() == 3 and ca.dim() >= 3 else 0
+        workspace = _workspace(ca.device, need)
+    return ext.decode(query, ca, cb, block_tables, seq_lens, out, workspace, 0 if peers is None else ctypes.addressof(peers))
 
 
 def paged_attention_decode(query: torch.Tensor, kv_cache: torch.Tensor, block_table: List[int], seq_len: int,
@@ -433,38 +326,28 @@ def paged_attention_prefill_chunk(query: torch.Tensor, kv_cache: KvCacheArg, blo
     """Causal attention of a query chunk ``[T, Hq, D]`` at positions ``[start_pos, start_pos + T)``
     over everything already in the cache for this sequence (history + the chunk itself, which the
     caller has written with ``reshape_and_cache``).  ``start_pos == 0`` is the reference prefill."""
-    desc, kplane = _describe_cache(kv_cache)
+    ca, cb = _split_cache(kv_cache)
     _require_cuda(query, "query")
     _require_cuda(block_table, "block_table")
-    if query.dim() != 3 or query.shape[2] != desc.head_dim or query.dtype != kplane.dtype:
+    if query.dim() != 3:
         raise ValueError("query must be [T, Hq, D] in the cache dtype")
-    t, hq, d = query.shape
-    if hq % desc.num_kv_heads:
-        raise ValueError("num_q_heads must be a multiple of num_kv_heads")
-    if query.stride(2) != 1 and d > 1:
+    if query.stride(2) != 1 and query.shape[2] > 1:
         query = query.contiguous()
-    bt = block_table.to(torch.int32).contiguous()
-    need_blocks = (start_pos + t + desc.block_size - 1) // desc.block_size
-    if bt.numel() < need_blocks:            # what the reference's block_table[i // BS] raises (paged_attention.py:119-123)
-        raise IndexError(f"block_table has {bt.numel()} entries, positions up to {start_pos + t} need {need_blocks}")
+    bt = block_table if block_table.dtype == torch.int32 and block_table.is_contiguous() else \
+        block_table.to(torch.int32).contiguous()
     if out is None:
-        out = torch.empty((t, hq, d), dtype=query.dtype, device=query.device)
-    lib = _lib.load()
-    need = lib.pa_prefill_workspace_bytes(t, hq, desc.num_kv_heads, d)
-    ws = _workspace(query.device, need)
-    with _DeviceOf(query):
-        rc = lib.pa_prefill(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0),
-                            out.stride(1), ctypes.byref(desc), bt.data_ptr(), start_pos, t, hq, ws.data_ptr(),
-                            ws.numel(), _stream_ptr())
-    _lib.check(rc, "pa_prefill")
+        out = torch.empty_like(query)
+    t, hq, d = query.shape
+    need = _lib.load().pa_prefill_workspace_bytes(t, hq, ca.shape[2] if ca.dim() >= 3 else 1, d)
+    _lib.load_ext().prefill_chunk(query, ca, cb, bt, int(start_pos), out, _workspace(query.device, need))
     return out
 
 
 def prefill_tensor_core_available(kv_cache: KvCacheArg, num_q_heads: int) -> bool:
     """True when prefill over this cache runs on the tcgen05 kernel (bf16, block_size 16,
     head_dim 64 / 128, g a power of two <= 16)."""
-    desc, _ = _describe_cache(kv_cache)
-    return bool(_lib.load().pa_prefill_tc_available(ctypes.byref(desc), num_q_heads))
+    ca, cb = _split_cache(kv_cache)
+    return bool(_lib.load_ext().prefill_tc_available(ca, cb, int(num_q_heads)))
 
 
 def paged_attention_prefill_varlen(query: torch.Tensor, kv_cache: KvCacheArg, block_tables: torch.Tensor,
@@ -480,46 +363,21 @@ def paged_attention_prefill_varlen(query: torch.Tensor, kv_cache: KvCacheArg, bl
     The lengths are device tensors, so a block-table row too short for its context cannot raise the
     reference's IndexError here without a host sync: the kernel skips such a request (its rows of ``out``
     are left alone) and never reads the table past ``block_tables.shape[1]``."""
-    desc, kplane = _describe_cache(kv_cache)
-    for name, ten in (("query", query), ("block_tables", block_tables), ("cu_q_lens", cu_q_lens),
-                      ("ctx_lens", ctx_lens)):
-        _require_cuda(ten, name)
-    if query.dim() != 3 or query.shape[2] != desc.head_dim or query.dtype != kplane.dtype:
-        raise ValueError("query must be [T, Hq, D] in the cache dtype")
-    if block_tables.dim() != 2 or block_tables.dtype != torch.int32 or block_tables.stride(1) != 1:
-        raise ValueError("block_tables must be int32 [B, max_blocks] with a contiguous last axis")
-    if cu_q_lens.dtype != torch.int32 or ctx_lens.dtype != torch.int32:
-        raise ValueError("cu_q_lens and ctx_lens must be int32")
-    b = block_tables.shape[0]
-    if cu_q_lens.numel() != b + 1 or ctx_lens.numel() != b:
-        raise ValueError("cu_q_lens must have B + 1 entries and ctx_lens B")
-    t, hq, d = query.shape
-    if hq % desc.num_kv_heads:
-        raise ValueError("num_q_heads must be a multiple of num_kv_heads")
-    if query.stride(2) != 1 and d > 1:
+    ca, cb = _split_cache(kv_cache)
+    _require_cuda(query, "query")
+    if query.dim() == 3 and query.stride(2) != 1 and query.shape[2] > 1:
         query = query.contiguous()
     if out is None:
-        out = torch.empty((t, hq, d), dtype=query.dtype, device=query.device)
-    if t == 0 or b == 0:
-        return out
-    lib = _lib.load()
-    cu = cu_q_lens.contiguous()
-    cl = ctx_lens.contiguous()
-    with _DeviceOf(query):
-        rc = lib.pa_prefill_varlen(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(),
-                                   out.stride(0), out.stride(1), ctypes.byref(desc), block_tables.data_ptr(),
-                                   block_tables.stride(0), block_tables.shape[1], cu.data_ptr(), cl.data_ptr(), b,
-                                   int(max_q_len), hq, _stream_ptr())
+        out = torch.empty_like(query)
+    rc = _lib.load_ext().prefill_varlen(query, ca, cb, block_tables, cu_q_lens, ctx_lens, int(max_q_len), out)
     if rc == -2:        # PA_ERR_UNSUPPORTED: not a tensor-core shape -> per-sequence CUDA path
-        cu_h = cu.tolist()
-        cl_h = cl.tolist()
-        for s in range(b):
+        cu_h = cu_q_lens.tolist()
+        cl_h = ctx_lens.tolist()
+        for s in range(block_tables.shape[0]):
             q0, q1 = cu_h[s], cu_h[s + 1]
             if q1 > q0:
                 paged_attention_prefill_chunk(query[q0:q1], kv_cache, block_tables[s], cl_h[s] - (q1 - q0),
                                               out=out[q0:q1])
-        return out
-    _lib.check(rc, "pa_prefill_varlen")
     return out
 
 
