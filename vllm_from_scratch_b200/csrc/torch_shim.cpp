@@ -30,7 +30,10 @@ void need_cuda_or_pinned(const Tensor& t, const char* name) {
               "device (or pin it for zero-copy access)");
 }
 void status(int rc, const char* what) {
-  TORCH_CHECK(rc == PA_OK, what, " failed: ", pa_status_string(rc), " (status ", rc, ")");
+  if (rc == PA_OK) return;
+  const char* text = pa_status_string(rc);
+  const std::string msg = std::string(what) + " failed: " + (text ? text : "?") + " (status " + std::to_string(rc) + ")";
+  TORCH_CHECK(false, msg);
 }
 
 // Either one tensor kv_cache[2, NB, Hkv, BS, D] ('hbsd', 01_paged_attention/paged_attention.py:26-30) or a pair
@@ -84,9 +87,13 @@ void reshape_and_cache(Tensor key, Tensor value, const Tensor& ca, const optiona
   if (value.strides() != key.strides()) { value = value.contiguous(); key = key.contiguous(); }
   const Tensor slots = slot_mapping.scalar_type() == at::kLong && slot_mapping.is_contiguous()
                            ? slot_mapping : slot_mapping.to(at::kLong).contiguous();
-  c10::cuda::CUDAGuard guard(ca.device());
-  status(pa_reshape_and_cache(key.data_ptr(), value.data_ptr(), key.stride(0), key.stride(1), &c,
-                              slots.data_ptr<int64_t>(), (int32_t)key.size(0), stream_of(ca)), "pa_reshape_and_cache");
+  int rc = PA_OK;
+  {
+    c10::cuda::CUDAGuard guard(ca.device());
+    rc = pa_reshape_and_cache(key.data_ptr(), value.data_ptr(), key.stride(0), key.stride(1), &c,
+                                slots.data_ptr<int64_t>(), (int32_t)key.size(0), stream_of(ca));
+  }
+  status(rc, "pa_reshape_and_cache");
 }
 
 // ---- fused RoPE + QKV split + KV slot write (pa_rope_and_cache) ---------------------------------------------
@@ -110,10 +117,14 @@ Tensor rope_and_cache(Tensor qkv, const Tensor& positions, Tensor cos_cached, Te
   const Tensor pos = positions.scalar_type() == at::kLong && positions.is_contiguous() ? positions : positions.to(at::kLong).contiguous();
   const Tensor slots = slot_mapping.scalar_type() == at::kLong && slot_mapping.is_contiguous()
                            ? slot_mapping : slot_mapping.to(at::kLong).contiguous();
-  c10::cuda::CUDAGuard guard(ca.device());
-  status(pa_rope_and_cache(qkv.data_ptr(), qkv.stride(0), (int32_t)num_q_heads, cos_cached.data_ptr(), sin_cached.data_ptr(),
-                           cos_cached.stride(0), (int32_t)cos_cached.size(0), pos.data_ptr<int64_t>(), slots.data_ptr<int64_t>(),
-                           (int32_t)t, out.data_ptr(), out.stride(0), out.stride(1), &c, stream_of(ca)), "pa_rope_and_cache");
+  int rc = PA_OK;
+  {
+    c10::cuda::CUDAGuard guard(ca.device());
+    rc = pa_rope_and_cache(qkv.data_ptr(), qkv.stride(0), (int32_t)num_q_heads, cos_cached.data_ptr(), sin_cached.data_ptr(),
+                             cos_cached.stride(0), (int32_t)cos_cached.size(0), pos.data_ptr<int64_t>(), slots.data_ptr<int64_t>(),
+                             (int32_t)t, out.data_ptr(), out.stride(0), out.stride(1), &c, stream_of(ca));
+  }
+  status(rc, "pa_rope_and_cache");
   return out;
 }
 
@@ -149,16 +160,20 @@ Tensor decode(Tensor query, const Tensor& ca, const optional<Tensor>& cb, Tensor
   const size_t need = pa_decode_workspace_bytes((int32_t)b, (int32_t)hq, c.num_kv_heads, (int32_t)d);
   const size_t have = (size_t)workspace.numel() * workspace.element_size();
   TORCH_CHECK_VALUE(workspace.is_cuda() && have >= need, "workspace must be a CUDA tensor of at least ", need, " bytes");
-  c10::cuda::CUDAGuard guard(ca.device());
-  if (peers_ptr == 0)
-    status(pa_decode(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1), &c,
-                     block_tables.data_ptr<int32_t>(), (int32_t)block_tables.stride(0), seq_lens.data_ptr<int32_t>(), (int32_t)b,
-                     (int32_t)hq, workspace.data_ptr(), have, stream_of(ca)), "pa_decode");
-  else
-    status(pa_decode_gather(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1), &c,
-                            block_tables.data_ptr<int32_t>(), (int32_t)block_tables.stride(0), seq_lens.data_ptr<int32_t>(),
-                            (int32_t)b, (int32_t)hq, workspace.data_ptr(), have,
-                            reinterpret_cast<const PaPeerGather*>(peers_ptr), stream_of(ca)), "pa_decode_gather");
+  int rc = PA_OK;
+  {
+    c10::cuda::CUDAGuard guard(ca.device());
+    if (peers_ptr == 0)
+      rc = pa_decode(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1), &c,
+                       block_tables.data_ptr<int32_t>(), (int32_t)block_tables.stride(0), seq_lens.data_ptr<int32_t>(), (int32_t)b,
+                       (int32_t)hq, workspace.data_ptr(), have, stream_of(ca));
+    else
+      rc = pa_decode_gather(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1), &c,
+                              block_tables.data_ptr<int32_t>(), (int32_t)block_tables.stride(0), seq_lens.data_ptr<int32_t>(),
+                              (int32_t)b, (int32_t)hq, workspace.data_ptr(), have,
+                              reinterpret_cast<const PaPeerGather*>(peers_ptr), stream_of(ca));
+  }
+  status(rc, peers_ptr == 0 ? "pa_decode" : "pa_decode_gather");
   return out;
 }
 
@@ -188,11 +203,14 @@ int64_t prefill_varlen(Tensor query, const Tensor& ca, const optional<Tensor>& c
   TORCH_CHECK_VALUE(query.stride(2) == 1 || query.size(2) <= 1, "query must have a contiguous last axis");
   if (query.size(0) == 0 || b == 0) return PA_OK;
   const Tensor cu = cu_q_lens.contiguous(), cl = ctx_lens.contiguous();
-  c10::cuda::CUDAGuard guard(query.device());
-  const int rc = pa_prefill_varlen(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1), &c,
-                                   block_tables.data_ptr<int32_t>(), (int32_t)block_tables.stride(0), (int32_t)block_tables.size(1),
-                                   cu.data_ptr<int32_t>(), cl.data_ptr<int32_t>(), (int32_t)b, (int32_t)max_q_len,
-                                   (int32_t)query.size(1), stream_of(query));
+  int rc = PA_OK;
+  {
+    c10::cuda::CUDAGuard guard(query.device());
+    rc = pa_prefill_varlen(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1), &c,
+                                     block_tables.data_ptr<int32_t>(), (int32_t)block_tables.stride(0), (int32_t)block_tables.size(1),
+                                     cu.data_ptr<int32_t>(), cl.data_ptr<int32_t>(), (int32_t)b, (int32_t)max_q_len,
+                                     (int32_t)query.size(1), stream_of(query));
+  }
   if (rc != PA_ERR_UNSUPPORTED) status(rc, "pa_prefill_varlen");
   return rc;
 }
@@ -212,10 +230,14 @@ void prefill_chunk(const Tensor& query, const Tensor& ca, const optional<Tensor>
   // what the reference's block_table[i // BS] raises (paged_attention.py:119-123)
   TORCH_CHECK_INDEX(block_table.numel() >= need_blocks, "block_table has ", block_table.numel(), " entries, positions up to ",
                     start_pos + t, " need ", need_blocks);
-  c10::cuda::CUDAGuard guard(query.device());
-  status(pa_prefill(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1), &c,
-                    block_table.data_ptr<int32_t>(), (int32_t)start_pos, (int32_t)t, (int32_t)query.size(1), workspace.data_ptr(),
-                    (size_t)workspace.numel() * workspace.element_size(), stream_of(query)), "pa_prefill");
+  int rc = PA_OK;
+  {
+    c10::cuda::CUDAGuard guard(query.device());
+    rc = pa_prefill(query.data_ptr(), query.stride(0), query.stride(1), out.data_ptr(), out.stride(0), out.stride(1), &c,
+                      block_table.data_ptr<int32_t>(), (int32_t)start_pos, (int32_t)t, (int32_t)query.size(1), workspace.data_ptr(),
+                      (size_t)workspace.numel() * workspace.element_size(), stream_of(query));
+  }
+  status(rc, "pa_prefill");
 }
 
 // ---- persistent block tables (pa_block_table_step) -----------------------------------------------------------------
@@ -256,9 +278,13 @@ void block_table_step(const Tensor& table, const optional<Tensor>& updates, cons
     st = step_table->data_ptr<int32_t>();
     st_stride = (int32_t)step_table->stride(0);
   }
-  c10::cuda::CUDAGuard guard(table.device());
-  status(pa_block_table_step(table.data_ptr<int32_t>(), (int32_t)table.stride(0), (int32_t)table.size(0), upd, nupd, max_upd, rows, lens,
-                             n_gather, (int32_t)block_size, st, st_stride, stream_of(table)), "pa_block_table_step");
+  int rc = PA_OK;
+  {
+    c10::cuda::CUDAGuard guard(table.device());
+    rc = pa_block_table_step(table.data_ptr<int32_t>(), (int32_t)table.stride(0), (int32_t)table.size(0), upd, nupd, max_upd, rows, lens,
+                               n_gather, (int32_t)block_size, st, st_stride, stream_of(table));
+  }
+  status(rc, "pa_block_table_step");
 }
 
 }  // namespace
