@@ -92,3 +92,8 @@ def test_torch_shim_loads_and_mirrors_the_error_contract():
                                          torch.ones(1, dtype=torch.int32), workspace=torch.zeros(8))
     with pytest.raises(TypeError):
         P.reshape_and_cache("not a tensor", torch.zeros(3, 2, 8), (k, k.clone()), torch.arange(3))
+    # c10 errors map to the host mirror's exception types (and never carry a C++ backtrace)
+    for kind, exc in ((0, RuntimeError), (1, ValueError), (2, TypeError), (3, IndexError), (4, RuntimeError)):
+        with pytest.raises(exc) as info:
+            ext._raise(kind, 7)
+        assert "frame #" not in str(info.value)

@@ -9,6 +9,7 @@
 // the ctypes path costs ~20 us of Python per call (descriptor building, argument marshalling, stream and
 // device lookups), this one ~3 us - the difference is most of an eager engine step at toy model sizes.
 #include <torch/extension.h>
+#include <torch/csrc/Exceptions.h>
 
 #include <c10/cuda/CUDAGuard.h>
 #include <c10/cuda/CUDAStream.h>
@@ -291,13 +292,24 @@ void block_table_step(const Tensor& table, const optional<Tensor>& updates, cons
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.doc() = "thin torch C++ extension over libpa_b200.so (include/pa_b200.h)";
+  // every function goes through torch::wrap_pybind_function: c10 errors become the matching Python exception
+  // (ValueError / TypeError / IndexError / RuntimeError) WITHOUT the C++ backtrace - pybind11's default translator
+  // calls what(), whose symbolised backtrace crashed the interpreter once a CUDA context was up
   m.def("abi_version", []() { return pa_abi_version(); });
-  m.def("reshape_and_cache", &reshape_and_cache);
-  m.def("rope_and_cache", &rope_and_cache);
-  m.def("decode", &decode);
-  m.def("decode_workspace_bytes", &decode_workspace_bytes);
-  m.def("prefill_tc_available", &prefill_tc_available);
-  m.def("prefill_varlen", &prefill_varlen);
-  m.def("prefill_chunk", &prefill_chunk);
-  m.def("block_table_step", &block_table_step);
+  // test hook: raise each exception kind the shim uses (tests/test_c_abi.py checks the Python types)
+  m.def("_raise", torch::wrap_pybind_function([](int64_t kind, int64_t n) {
+    if (kind == 0) TORCH_CHECK(false, "runtime ", n);
+    if (kind == 1) TORCH_CHECK_VALUE(false, "value ", n);
+    if (kind == 2) TORCH_CHECK_TYPE(false, "type ", n);
+    if (kind == 3) TORCH_CHECK_INDEX(false, "index ", n, " of ", n + 1);
+    if (kind == 4) status(-3, "pa_test");
+  }));
+  m.def("reshape_and_cache", torch::wrap_pybind_function(reshape_and_cache));
+  m.def("rope_and_cache", torch::wrap_pybind_function(rope_and_cache));
+  m.def("decode", torch::wrap_pybind_function(decode));
+  m.def("decode_workspace_bytes", torch::wrap_pybind_function(decode_workspace_bytes));
+  m.def("prefill_tc_available", torch::wrap_pybind_function(prefill_tc_available));
+  m.def("prefill_varlen", torch::wrap_pybind_function(prefill_varlen));
+  m.def("prefill_chunk", torch::wrap_pybind_function(prefill_chunk));
+  m.def("block_table_step", torch::wrap_pybind_function(block_table_step));
 }
