@@ -43,12 +43,13 @@ class _Sched:
     slot_mapping: List[int]
 
 
-def _random_history(ops, device, steps=120, seed=0, max_seqs=4, max_blocks=4, max_tokens=8):
+def _random_history(ops, device, steps=120, seed=0, max_seqs=4, max_blocks=4, max_tokens=8, token_tables=False):
     """Drive StepTables with a random scheduler: new requests, decode tokens, prefill chunks, block replacement
     (swap-in), requests that disappear for a while (row eviction) and more requests / longer tables than the
     initial capacity (growth).  After every step the device tables are compared with the lists."""
     rng = random.Random(seed)
-    tables = engine_adapter.StepTables(device, ops, BS, max_seqs=max_seqs, max_tokens=max_tokens, max_blocks=max_blocks)
+    tables = engine_adapter.StepTables(device, ops, BS, max_seqs=max_seqs, max_tokens=max_tokens, max_blocks=max_blocks,
+                                       token_tables=token_tables)
     live: List[_Req] = []
     next_block, nreq = 0, 0
     generations = set()
@@ -108,6 +109,17 @@ def _random_history(ops, device, steps=120, seed=0, max_seqs=4, max_blocks=4, ma
         for (off, n, start, row), s in zip(md.prefill_chunks, [s for s in scheduled if s.is_prefill]):
             assert (n, start) == (len(s.tokens), s.positions[0])
             assert row[:(start + n + BS - 1) // BS].tolist() == s.request.block_table[:(start + n + BS - 1) // BS]
+        if token_tables:
+            # per-token form: token t of a request is a decode "sequence" of length position + 1 over the request's table
+            tt = md.tok_block_tables.cpu()
+            want_lens = [p + 1 for s in scheduled for p in s.positions]
+            assert md.tok_ctx_lens.tolist() == want_lens
+            at = 0
+            for s in scheduled:
+                for p in s.positions:
+                    need = (p + 1 + BS - 1) // BS
+                    assert tt[at, :need].tolist() == s.request.block_table[:need]
+                    at += 1
         # padding invariant the decode graphs rely on: beyond the batch rows are -1 / lengths 0 / slots -1
         b, t = len(scheduled), cu[-1]
         assert (tables.dv["row_of"][b:tables.cap].cpu() == -1).all()
@@ -120,6 +132,11 @@ def test_step_tables_random_history_cpu():
     tables, generations = _random_history(OracleOps, "cpu")
     assert len(generations) > 1, "the history never outgrew the initial capacity"
     assert tables.cap >= 6 and tables.W > 4
+
+
+def test_step_tables_per_token_form_cpu():
+    tables, generations = _random_history(OracleOps, "cpu", seed=5, token_tables=True)
+    assert tables.token_tables and len(generations) > 1
 
 
 def test_step_tables_ship_only_the_delta_cpu():
@@ -210,6 +227,8 @@ def test_step_tables_random_history_cuda():
     from vllm_from_scratch_b200 import paged_attention as P
     tables, generations = _random_history(P, "cuda", steps=150, seed=3)
     assert len(generations) > 1
+    tables, generations = _random_history(P, "cuda", steps=100, seed=4, token_tables=True)
+    assert tables.token_tables and len(generations) > 1
 
 
 def _run(device, ops, graphs, prompts, dtype=torch.float32, new_tokens=12, **kw):

@@ -79,6 +79,10 @@ class StepMetadata:
     positions: Optional[torch.Tensor] = None                 # int64 [T]
     slot_mapping: Optional[torch.Tensor] = None              # int64 [T]
     last_idx: Optional[torch.Tensor] = None                  # int64 [B] index of each request's last token
+    # per-TOKEN form for shapes outside the tensor-core prefill kernel: token t is a decode "sequence" of length
+    # position + 1 over its request's table, so a whole mixed step is ONE generic decode launch
+    tok_block_tables: Optional[torch.Tensor] = None          # int32 [T, max_blocks]
+    tok_ctx_lens: Optional[torch.Tensor] = None              # int32 [T]
 
 
 class StepTables:
@@ -94,10 +98,14 @@ class StepTables:
     _I32 = ("hdr", "row_of", "gather_lens", "cu_q_lens", "ctx_pf")
     _I64 = ("decode_rows", "last_idx", "tokens", "positions", "slots")
 
-    def __init__(self, device, ops, block_size: int, max_seqs: int = 16, max_tokens: int = 256, max_blocks: int = 64):
+    TOKEN_TABLE_LIMIT = 4 << 20     # entries of the per-token table (16 MiB); beyond it that form is switched off
+
+    def __init__(self, device, ops, block_size: int, max_seqs: int = 16, max_tokens: int = 256, max_blocks: int = 64,
+                 token_tables: bool = False):
         self.device = torch.device(device)
         self.ops = ops
         self.block_size = int(block_size)
+        self.token_tables = bool(token_tables)
         self.generation = 0
         self.step_no = 0
         self.updates_sent = 0                                   # block-table entries shipped so far (tests, stats)
@@ -109,14 +117,17 @@ class StepTables:
         self.ucap = max(ucap, 1024, 8 * cap)
         self.rows = 2 * cap
         dev = self.device
+        if self.token_tables and tcap * width > self.TOKEN_TABLE_LIMIT:
+            self.token_tables = False
+        ntok = tcap if self.token_tables else 0                 # gathered rows: [requests | decode requests | tokens]
         self.table = torch.zeros(self.rows, width, dtype=torch.int32, device=dev)
-        self.step_tables = torch.zeros(2 * cap, width, dtype=torch.int32, device=dev)
+        self.step_tables = torch.zeros(2 * cap + ntok, width, dtype=torch.int32, device=dev)
         self.mirror: List[List[int]] = [[] for _ in range(self.rows)]
         self.key_of_row: List[Any] = [None] * self.rows
         self.row_of_key: Dict[Any, int] = {}
         self.last_used = [0] * self.rows
         self.free_rows = list(range(self.rows - 1, -1, -1))
-        sizes = {"hdr": 4, "row_of": 2 * cap, "gather_lens": 2 * cap, "cu_q_lens": cap + 1, "ctx_pf": cap,
+        sizes = {"hdr": 4, "row_of": 2 * cap + ntok, "gather_lens": 2 * cap + ntok, "cu_q_lens": cap + 1, "ctx_pf": cap,
                  "decode_rows": cap, "last_idx": cap, "tokens": tcap, "positions": tcap, "slots": tcap}
         off, at = {}, 0
         for name in self._I32:
@@ -203,6 +214,8 @@ class StepTables:
         pos: List[int] = []
         slots: List[int] = []
         upd: List[int] = []
+        tok_rows: List[int] = []
+        tok_lens: List[int] = []
         for sched in scheduled:
             req = sched.request
             n = len(sched.tokens)
@@ -248,6 +261,9 @@ class StepTables:
             toks += sched.tokens
             pos += sched.positions
             slots += sched.slot_mapping
+            if self.token_tables:
+                tok_rows += [row] * n
+                tok_lens += range(start + 1, start + n + 1)
         nupd = len(upd) // 3
         if nupd > self.ucap:
             for row in rows:                                    # the delta was not shipped: forget it
@@ -280,6 +296,11 @@ class StepTables:
         hv["positions"][t:max(t, pt)] = 0
         hv["slots"][:t] = slots
         hv["slots"][t:max(t, pt)] = -1
+        if self.token_tables:
+            hv["row_of"][2 * cap:2 * cap + t] = tok_rows
+            hv["row_of"][2 * cap + t:2 * cap + max(t, pt)] = -1
+            hv["gather_lens"][2 * cap:2 * cap + t] = tok_lens
+            hv["gather_lens"][2 * cap + t:2 * cap + max(t, pt)] = 0
         if nupd:
             hv["updates"].reshape(-1)[:3 * nupd] = upd
         self._prev[which] = (b, bd, t)
@@ -298,6 +319,9 @@ class StepTables:
         md.max_q_len = max(md.num_tokens)
         md.token_ids, md.positions, md.slot_mapping = dv["tokens"][:t], dv["positions"][:t], dv["slots"][:t]
         md.last_idx = dv["last_idx"][:b]
+        if self.token_tables:
+            md.tok_block_tables = self.step_tables[2 * cap:2 * cap + t]
+            md.tok_ctx_lens = dv["gather_lens"][2 * cap:2 * cap + t]
         if bd:
             md.decode_rows = dv["decode_rows"][:bd]
             md.decode_block_tables = self.step_tables[:b] if md.all_decode else self.step_tables[cap:cap + bd]
@@ -408,6 +432,11 @@ def _attend(attn, ops, state, md: StepMetadata, q, cache, t, h, d):
         # tensor-core shapes: the whole mixed step (prefill chunks + decode tokens) in ONE launch
         out = varlen(q, cache, md.all_block_tables, md.cu_q_lens, md.ctx_lens, md.max_q_len)
         return attn.out_proj(out.reshape(t, h * d))
+    if md.tok_block_tables is not None and can_decode:
+        # every other shape (fp32, toy head sizes): each token is a decode "sequence" of length position + 1 over its
+        # request's table - the whole mixed step in ONE generic decode launch instead of one per prefill chunk
+        out = _decode(ops, state, q, cache, md.tok_block_tables, md.tok_ctx_lens)
+        return attn.out_proj(out.reshape(t, h * d))
     out = torch.empty((t, h, d), dtype=q.dtype, device=q.device)
     if md.decode_rows is not None:
         q_dec = q.index_select(0, md.decode_rows)
@@ -513,16 +542,21 @@ def install(engine: Any, ops: Any = None, cuda_graphs: Optional[bool] = None) ->
     device = torch.device(engine.device)
     sched = engine.scheduler
     block_size = int(engine.model.k_cache.shape[2])
+    a0 = layers[0].attn
+    # shapes the tcgen05 varlen kernel does not take run a mixed step as one generic decode launch over per-token tables
+    tc_fn = getattr(ops, "prefill_tensor_core_available", None)
+    tc = False
+    if tc_fn is not None and device.type == "cuda":
+        tc = bool(tc_fn((engine.model.k_cache[0], engine.model.v_cache[0]), a0.num_heads))
     tables = StepTables(device, ops, block_size, getattr(sched, "max_num_seqs", 16),
-                        getattr(sched, "max_num_batched_tokens", 256), 64)
+                        getattr(sched, "max_num_batched_tokens", 256), 64,
+                        token_tables=not tc and hasattr(ops, "paged_attention_decode_batched"))
     state = {"ops": ops, "meta": None, "orig_schedule": sched.schedule, "tables": tables, "workspace": None,
              "workspace_cap": 0, "orig_forwards": [layer.attn.forward for layer in layers], "graphs": None,
              "orig_model_forward": None}
     engine._pa_b200 = state
-    a0 = layers[0].attn
-
     def new_workspace():
-        state["workspace_cap"] = max(tables.cap, 64)
+        state["workspace_cap"] = max(tables.cap, tables.tcap if tables.token_tables else 0, 64)
         state["workspace"] = ops.new_decode_workspace(state["workspace_cap"], a0.num_heads, a0.num_heads, a0.head_dim,
                                                       device)
 
@@ -532,7 +566,7 @@ def install(engine: Any, ops: Any = None, cuda_graphs: Optional[bool] = None) ->
     def schedule_with_metadata():
         scheduled = state["orig_schedule"]()
         state["meta"] = tables.build(scheduled) if scheduled else None
-        if state["workspace"] is not None and tables.cap > state["workspace_cap"]:
+        if state["workspace"] is not None and max(tables.cap, tables.tcap if tables.token_tables else 0) > state["workspace_cap"]:
             new_workspace()
             tables.generation += 1                              # captured graphs hold the old workspace
         return scheduled
