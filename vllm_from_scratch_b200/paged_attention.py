@@ -466,6 +466,7 @@ def copy_blocks(cache: Union[torch.Tensor, Sequence[torch.Tensor]], src_dst, blo
     if n == 0:
         return
     lib = _lib.load()
+    launches = []           # (tensor for the device guard, base pointer, plane stride, planes, block stride, block bytes, pairs)
     for c in caches:
         _require_cuda(c, "cache")
         bd = c.dim() - 4 if block_dim is None else block_dim
@@ -479,11 +480,22 @@ def copy_blocks(cache: Union[torch.Tensor, Sequence[torch.Tensor]], src_dst, blo
                 pairs_dev = torch.tensor(pl, dtype=torch.int64).to(c.device)
             by_device[c.device] = pairs_dev
         block_bytes, block_stride, groups = _plane_groups(c, bd)
+        for off, planes, pstride in groups:
+            launches.append([c, c.data_ptr() + off, pstride, planes, block_stride, block_bytes, pairs_dev])
+    # Two single-plane groups of identical geometry (the engine's (k_cache, v_cache) pair, each [NB, BS, H, D]) are
+    # two planes at a constant distance: ONE launch instead of two short ones (each pays its own ramp and tail).
+    merged = []
+    for ln in launches:
+        prev = merged[-1] if merged else None
+        if prev is not None and prev[3] == 1 and ln[3] == 1 and prev[4:6] == ln[4:6] and prev[6] is ln[6] \
+                and prev[0].device == ln[0].device and ln[1] > prev[1] and (ln[1] - prev[1]) % 16 == 0:
+            prev[2], prev[3] = ln[1] - prev[1], 2
+        else:
+            merged.append(ln)
+    for c, base, pstride, planes, block_stride, block_bytes, pairs_dev in merged:
         with _DeviceOf(c):
-            for off, planes, pstride in groups:
-                rc = lib.pa_copy_blocks(c.data_ptr() + off, pstride, planes, block_stride, block_bytes,
-                                        pairs_dev.data_ptr(), n, _stream_ptr())
-                _lib.check(rc, "pa_copy_blocks")
+            rc = lib.pa_copy_blocks(base, pstride, planes, block_stride, block_bytes, pairs_dev.data_ptr(), n, _stream_ptr())
+            _lib.check(rc, "pa_copy_blocks")
 
 
 class HostKVPool(BlockFifo):
