@@ -320,10 +320,15 @@ def head_sharded_section(torch, dist, P, S, dev, world, rank, steps, timer):
         ws = P.new_decode_workspace(b, hq, hkv, d, dev)
         out_full = torch.empty_like(q)
         caches = [pool.layer(i) for i in range(layers)]
-        graphs = capture_steps(torch, lambda i: P.paged_attention_decode_batched(q, caches[i], bts, lens, out=out_full, workspace=ws), layers)
-        for i in range(3 * layers):
-            graphs[i % layers].replay()
-        ms1, _, _ = timer.run(lambda i: graphs[i % layers].replay(), steps)
+        # every arm is timed the same way: ONE CUDA graph holds a round over the layer caches (programmatic
+        # dependent-launch edges kept, one host launch per round); `rounds` replays = rounds * layers steps
+        rounds = max(steps // layers, 2)
+        nsteps = rounds * layers
+        graphs = capture_steps(torch, lambda i: P.paged_attention_decode_batched(q, caches[i], bts, lens, out=out_full, workspace=ws),
+                               layers, one_graph=True)
+        for i in range(3):
+            graphs[0].replay()
+        ms1, _, _ = timer.run(lambda i: graphs[0].replay(), rounds)
         ref_full = P.paged_attention_decode_batched(q, caches[0], bts, lens).clone()
         kvh, qh = S.shard_kv_heads(hkv, world, rank), S.shard_q_heads(hq, hkv, world, rank)
         local = pool.kv_cache[:, :, :, kvh.start:kvh.stop].contiguous()                             # [2, L, NB, Hkv / N, BS, D]
@@ -346,15 +351,16 @@ def head_sharded_section(torch, dist, P, S, dev, world, rank, steps, timer):
         ok_bits = torch.equal(got, want)
         ok_full = strict_close(pg.full(got), ref_full)
         pg.decode(q_l, lcaches[1], bts, lens, workspace=ws_l, parity=1)                             # keep the parity sequence 0, 1, 0, 1 ...
-        pgraphs = capture_steps(torch, lambda i: pg.decode(q_l, lcaches[i], bts, lens, workspace=ws_l, parity=i % 2), layers)
-        for i in range(3 * layers):
-            pgraphs[i % layers].replay()
-        # lead must keep the 0 / 1 alternation: `lead` = layers (even)
-        ms_p, _, _ = timer.run(lambda i: pgraphs[i % layers].replay(), steps - steps % layers, lead=layers)
+        # a round = `layers` (even) steps: the 0 / 1 buffer-set alternation is preserved across replays
+        pgraphs = capture_steps(torch, lambda i: pg.decode(q_l, lcaches[i], bts, lens, workspace=ws_l, parity=i % 2), layers,
+                                one_graph=True)
+        for i in range(3):
+            pgraphs[0].replay()
+        ms_p, _, _ = timer.run(lambda i: pgraphs[0].replay(), rounds)
         pg.check()
-        arms["peer_ll"] = (ms_p / (steps - steps % layers), ok_bits and ok_full,
+        arms["peer_ll"] = (ms_p / nsteps, ok_bits and ok_full,
                            "gather fused into the decode kernel: NVLink peer stores of {data, step} words, receive kernel; "
-                           "decode + receive replayed as one CUDA graph per layer cache")
+                           "decode + receive of a whole round over the layer caches replayed as one CUDA graph")
         pg.close()
         # ---- NCCL arm: the same decode kernel writes its slice in place + one all_gather_into_tensor ----
         hg = S.HeadGather(b, hq, d, torch.bfloat16, dev, world=world, rank=rank)
@@ -368,17 +374,20 @@ def head_sharded_section(torch, dist, P, S, dev, world, rank, steps, timer):
         ok_n = torch.equal(hg.buf, want) and strict_close(hg.full(), ref_full)
         how = "eager launches"
         try:
-            ngraphs = capture_steps(torch, nccl_step, layers)
-            run_n = lambda i: ngraphs[i % layers].replay()                                          # noqa: E731
-            how = "decode + all_gather replayed as one CUDA graph per layer cache"
+            ngraphs = capture_steps(torch, nccl_step, layers, one_graph=True)
+            run_n = lambda i: ngraphs[0].replay()                                                   # noqa: E731
+            how = "decode + all_gather of a whole round over the layer caches replayed as one CUDA graph"
         except Exception:                                                                           # noqa: BLE001 - capture of the collective refused: time it eagerly
             torch.cuda.synchronize()
-            run_n = nccl_step
-        for i in range(3 * layers):
+
+            def run_n(i):
+                for j in range(layers):
+                    nccl_step(j)
+        for i in range(3):
             run_n(i)
-        ms_n, _, _ = timer.run(run_n, steps)
-        arms["nccl"] = (ms_n / steps, ok_n, "decode kernel + one NCCL all_gather_into_tensor of [B, Hq/N, D]; " + how)
-        ms1_max, = timer.max_over_ranks([ms1 / steps], dev)
+        ms_n, _, _ = timer.run(run_n, rounds)
+        arms["nccl"] = (ms_n / nsteps, ok_n, "decode kernel + one NCCL all_gather_into_tensor of [B, Hq/N, D]; " + how)
+        ms1_max, = timer.max_over_ranks([ms1 / nsteps], dev)
         entry["one_gpu_us_per_step"] = ms1_max * 1e3
         for aname, (ms, okv, what) in arms.items():
             ms_max, bad = timer.max_over_ranks([ms, 0.0 if okv else 1.0], dev)
