@@ -210,7 +210,11 @@ int pa_block_table_step(int32_t* table, int32_t table_stride, int32_t num_rows,
  *      :119-123, and the scatter mini_vllm.py:424-427) ----------------------
  * key/value [num_tokens, Hkv, D] with token / head strides in elements.
  * slot_mapping int64 [num_tokens]: slot = block*BS + offset; slot < 0 skips
- * the token (padding).  Pure byte copy: bit-exact.                           */
+ * the token (padding).  Pure byte copy: bit-exact.
+ * Out-of-range input (no host sync is possible on this path): a slot >=
+ * NB*BS is skipped like a negative one - the reference's index_put would
+ * raise IndexError (mini_vllm.py:424-427); the host mirror's scheduler-side
+ * slot computation (compute_slot_mapping) is where that error is raised.     */
 int pa_reshape_and_cache(const void* key, const void* value,
                          int64_t kv_stride_token, int64_t kv_stride_head,
                          const PaKvCache* cache,
@@ -225,7 +229,10 @@ int pa_reshape_and_cache(const void* key, const void* value,
  *   [max_positions, D] are the module's own cached tables (cos_cached /
  *   sin_cached, :366-370) in the same dtype; positions int64 [num_tokens].
  * Writes rotated Q to q_out [num_tokens, Hq, D], rotated K and plain V to the
- *   cache slots (slot < 0 skips the cache write).  Rounds exactly where torch's
+ *   cache slots (slot < 0 or >= NB*BS skips the cache write; a position outside
+ *   [0, max_positions) is clamped into the table where the reference's table
+ *   gather would raise - positions come from the scheduler, which bounds them).
+ *   Rounds exactly where torch's
  *   op-by-op evaluation rounds (no FMA contraction): bit-exact in fp32 and bf16. */
 int pa_rope_and_cache(const void* qkv, int64_t qkv_stride_t, int32_t num_q_heads,
                       const void* cos_table, const void* sin_table,
