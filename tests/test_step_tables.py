@@ -252,7 +252,8 @@ def test_decode_graphs_match_eager_engine(cfg):
     b, rb = _run("cuda", None, True, prompts, **kw)
     g = b._pa_b200["graphs"]
     assert a._pa_b200["graphs"] is None and g is not None
-    assert g.replays >= 10 and g.captures == 4, (g.replays, g.captures)      # buckets 1, 2, 4, 8
+    assert g.replays >= 10 and g.captures >= 4, (g.replays, g.captures)      # decode buckets 1, 2, 4, 8 + mixed buckets
+    assert any(k[2] for k in g.graphs), "no mixed chunked-prefill + decode step was replayed from a graph"
     tol = 1e-4 if cfg["dtype"] == torch.float32 else 6e-2
     same = 0
     for x, y in zip(ra, rb):

@@ -336,18 +336,29 @@ class StepTables:
             md.ctx_lens_prefill_only = dv["ctx_pf"][:b]
         return md
 
-    def padded(self, bucket: int) -> StepMetadata:
-        """The decode-only metadata of a ``bucket``-request step at the staging mirror's fixed addresses
-        (what a CUDA graph is captured over): requests past the real batch have context length 0."""
+    def padded(self, bucket: int, tokens: int = 0, mixed: bool = False) -> StepMetadata:
+        """The metadata of a padded step at the staging mirror's fixed addresses (what a CUDA graph is captured
+        over): ``bucket`` requests, and ``tokens`` >= ``bucket`` tokens for a mixed step (0: a step whose requests
+        all feed one token).  Requests / tokens past the real ones have context length 0, row -1, slot -1."""
         dv = self.dv
-        md = StepMetadata(num_tokens=[1] * bucket, start_pos=[0] * bucket, is_prefill=[False] * bucket,
-                          block_tables=[[]] * bucket, all_decode=True)
-        md.all_block_tables = md.decode_block_tables = self.step_tables[:bucket]
-        md.ctx_lens = md.decode_ctx_lens = dv["gather_lens"][:bucket]
+        cap = self.cap
+        t = max(tokens, bucket) if mixed else bucket
+        # any token split of the right total will do: only the totals shape the captured launches
+        md = StepMetadata(num_tokens=[t - bucket + 1] + [1] * (bucket - 1), start_pos=[0] * bucket,
+                          is_prefill=[mixed] + [False] * (bucket - 1), block_tables=[[]] * bucket, all_decode=not mixed)
+        md.all_block_tables = self.step_tables[:bucket]
+        md.ctx_lens = dv["gather_lens"][:bucket]
         md.cu_q_lens = dv["cu_q_lens"][:bucket + 1]
-        md.decode_rows = dv["decode_rows"][:bucket]
-        md.max_q_len = 1
-        md.token_ids, md.positions, md.slot_mapping = dv["tokens"][:bucket], dv["positions"][:bucket], dv["slots"][:bucket]
+        md.max_q_len = t - bucket + 1 if mixed else 1
+        if not mixed:
+            md.decode_block_tables, md.decode_ctx_lens = md.all_block_tables, md.ctx_lens
+            md.decode_rows = dv["decode_rows"][:bucket]
+        elif self.token_tables:
+            md.tok_block_tables = self.step_tables[2 * cap:2 * cap + t]
+            md.tok_ctx_lens = dv["gather_lens"][2 * cap:2 * cap + t]
+        else:
+            md.max_q_len = t                                    # varlen launch: any chunk length up to the bucket
+        md.token_ids, md.positions, md.slot_mapping = dv["tokens"][:t], dv["positions"][:t], dv["slots"][:t]
         md.last_idx = dv["last_idx"][:bucket]
         return md
 
@@ -454,24 +465,39 @@ _MODEL_ATTRS = ("embedding", "layers", "norm", "lm_head", "k_cache", "v_cache")
 
 
 class DecodeGraphs:
-    """Decode-only steps as CUDA graphs, one per batch-size bucket (1, 2, 4, ... max_num_seqs).
+    """Engine steps as CUDA graphs: decode-only steps, one graph per batch-size bucket (1, 2, 4, ...
+    max_num_seqs), and mixed chunked-prefill + decode steps, one per (token bucket, request bucket).
 
     What is captured is the reference model's own forward (mini_vllm.py:592-613: embedding -> layers ->
     norm -> last-token rows -> lm_head) over the reference's own modules, with its inputs read from
     ``StepTables``' staging mirror (fixed addresses) and the last-token rows selected by a device index
     instead of a Python list (a list would be baked into the graph).  A replayed step therefore costs the
     host one staging fill, one H2D copy, the table step and ONE graph launch instead of ~15 launches per
-    layer.  Padded requests (row -1, context 0, slot -1) are no-ops for every kernel."""
+    layer.  Padded requests and tokens (row -1, context 0, slot -1) are no-ops for every kernel.  A mixed
+    step is capturable because it is ONE attention launch whatever its composition: the tcgen05 varlen kernel
+    on tensor-core shapes, the generic decode kernel over per-token tables elsewhere."""
 
-    def __init__(self, engine, state):
+    def __init__(self, engine, state, mixed: bool = True):
         self.engine, self.state = engine, state
-        self.graphs: Dict[int, tuple] = {}
+        self.graphs: Dict[tuple, tuple] = {}
         self.generation = -1
         self.replays = 0
         self.captures = 0
+        self.mixed = mixed
 
     def usable(self, md: Optional[StepMetadata]) -> bool:
-        return md is not None and md.all_decode and len(md.num_tokens) <= self.state["tables"].cap
+        tables: StepTables = self.state["tables"]
+        if md is None or len(md.num_tokens) > tables.cap:
+            return False
+        if md.all_decode:
+            return True
+        if not self.mixed or sum(md.num_tokens) > tables.tcap:
+            return False
+        if tables.token_tables:
+            return True
+        # tensor-core shapes: one varlen launch - unless the decode rows stream enough KV for the split route
+        h, d = self.state["heads"], self.state["head_dim"]
+        return self.state["tc"] and md.decode_kv_tokens * 2 * h * d * 2 < SPLIT_DECODE_BYTES
 
     def _body(self, md: StepMetadata):
         m = self.engine.model
@@ -480,37 +506,45 @@ class DecodeGraphs:
             x = layer(x, md.positions, (m.k_cache[i], m.v_cache[i]), md.slot_mapping, md.num_tokens, md.is_prefill)
         return m.lm_head(m.norm(x).index_select(0, md.last_idx))
 
+    @staticmethod
+    def _bucket(n: int, cap: int) -> int:
+        k = 1
+        while k < n:
+            k *= 2
+        return min(k, cap)
+
     def run(self, md: StepMetadata) -> torch.Tensor:
         tables: StepTables = self.state["tables"]
         if self.generation != tables.generation:                # the staging mirror moved: captured addresses are stale
             self.graphs.clear()
             self.generation = tables.generation
         b = len(md.num_tokens)
-        bucket = 1
-        while bucket < b:
-            bucket *= 2
-        bucket = min(bucket, tables.cap)
-        entry = self.graphs.get(bucket)
-        if entry is None:
-            # first decode-only step (or the mirror moved): capture EVERY bucket now, so that no later step
-            # stalls on a capture (~5 ms each, more when cuBLAS meets a new shape); padded requests are no-ops
-            # and the step's own K / V rows are written with the same values by each warm-up pass
-            k = 1
-            while k < tables.cap:
-                if k not in self.graphs:
-                    self._capture(k)
-                k *= 2
-            if tables.cap not in self.graphs:
-                self._capture(tables.cap)
-            entry = self.graphs[bucket]
-        graph, logits = entry
+        bk = self._bucket(b, tables.cap)
+        if md.all_decode:
+            key = (bk, bk, False)
+            if key not in self.graphs:
+                # first decode-only step (or the mirror moved): capture EVERY decode bucket now, so that no later
+                # step stalls on a capture (~5 ms each, more when cuBLAS meets a new shape); padded requests are
+                # no-ops and the step's own K / V rows are written with the same values by each warm-up pass
+                k = 1
+                while k < tables.cap:
+                    if (k, k, False) not in self.graphs:
+                        self._capture((k, k, False))
+                    k *= 2
+                if (tables.cap, tables.cap, False) not in self.graphs:
+                    self._capture((tables.cap, tables.cap, False))
+        else:
+            key = (max(self._bucket(sum(md.num_tokens), tables.tcap), bk), bk, True)
+            if key not in self.graphs:
+                self._capture(key)
+        graph, logits = self.graphs[key]
         graph.replay()
         self.replays += 1
         return logits[:b]
 
-    def _capture(self, bucket: int):
+    def _capture(self, key: tuple):
         tables: StepTables = self.state["tables"]
-        md_k = tables.padded(bucket)
+        md_k = tables.padded(key[1], key[0], key[2])
         live = self.state["meta"]
         self.state["meta"] = md_k
         try:
@@ -525,7 +559,7 @@ class DecodeGraphs:
                     logits = self._body(md_k)
         finally:
             self.state["meta"] = live
-        self.graphs[bucket] = (graph, logits)
+        self.graphs[key] = (graph, logits)
         self.captures += 1
         return graph, logits
 
@@ -553,7 +587,7 @@ def install(engine: Any, ops: Any = None, cuda_graphs: Optional[bool] = None) ->
                         token_tables=not tc and hasattr(ops, "paged_attention_decode_batched"))
     state = {"ops": ops, "meta": None, "orig_schedule": sched.schedule, "tables": tables, "workspace": None,
              "workspace_cap": 0, "orig_forwards": [layer.attn.forward for layer in layers], "graphs": None,
-             "orig_model_forward": None}
+             "orig_model_forward": None, "tc": tc, "heads": a0.num_heads, "head_dim": a0.head_dim}
     engine._pa_b200 = state
     def new_workspace():
         state["workspace_cap"] = max(tables.cap, tables.tcap if tables.token_tables else 0, 64)
@@ -590,7 +624,8 @@ def install(engine: Any, ops: Any = None, cuda_graphs: Optional[bool] = None) ->
 
         def model_forward(token_ids, positions, slot_mapping, seq_lens, is_prefill):
             md = state["meta"]
-            if graphs.usable(md) and md.num_tokens == [int(s) for s in seq_lens] and not any(is_prefill):
+            if graphs.usable(md) and md.num_tokens == [int(s) for s in seq_lens] \
+                    and md.is_prefill == [bool(p) for p in is_prefill]:
                 return graphs.run(md)
             return state["orig_model_forward"](token_ids, positions, slot_mapping, seq_lens, is_prefill)
 
