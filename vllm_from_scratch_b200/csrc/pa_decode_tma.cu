@@ -347,7 +347,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   // threads x 96 registers = 61440 - not the SM's 64 Ki (asking for more blocks forever).  The producers'
   // single active lane needs next to nothing; what they give back goes to the consumers (fragments of Q,
   // the O accumulator, K / V fragment sets in flight) and to the finishers (8 partials' loads in flight per
-  // lane): 256 x 144 + 256 x 32 + 128 x 128 = 61440.
+  // lane): 256 x 144 + 256 x 24 + 128 x 144 = 61440.
   // Each role's code sits entirely inside the branch that executes its setmaxnreg (ptxas only grants the
   // larger budget to code dominated by the instruction), so the one CTA-wide barrier is issued per branch.
   auto cta_sync = [] { asm volatile("bar.sync 0, %0;" ::"n"(kThreads) : "memory"); };
@@ -378,7 +378,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   __nv_bfloat16* obase = static_cast<__nv_bfloat16*>(p.out);
 
   if (warp >= kSchedWarp) {
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 160;");
   if (warp == kSchedWarp) {
     // =========================== scheduler warp ==========================================
     // The plan and the first unit are prepared BEFORE the CTA-wide barrier below: nothing here needs the
@@ -762,7 +762,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     // descriptor ring, takes the next free stage of the consumer's private ring and issues the block's two
     // tensor loads.  Waiting here - for a descriptor, for a free stage, or in the issue path itself when
     // the memory system pushes back - delays nobody's math.
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 32;");
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
     pdl_wait();
     cta_sync();                                                // mbarriers are initialised
     if (lane != 0) return;
@@ -799,7 +799,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
   }
 
   // ============================= consumer warps ============================================
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 144;");
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 136;");
   pdl_wait();
   cta_sync();                                                  // mbarriers are initialised
   const uint32_t my_ring = smem_base + L.ring + warp * (R * STAGE_BYTES);
@@ -1076,7 +1076,7 @@ int get_map(const void* base, const PaDecodeParams& p, CUtensorMap* out, int* po
   key.nb = p.num_blocks;
   if (cudaGetDevice(&key.dev) != cudaSuccess) { cudaGetLastError(); key.dev = -1; }
   static_assert(sizeof(MapKey) % 8 == 0, "hashed as 64-bit words");
-  static_assert(kThreads * 96 == 256 * 144 + 256 * 32 + 128 * 128, "setmaxnreg budgets must add up to the launch allocation");
+  static_assert(kThreads * 96 == 256 * 136 + 256 * 24 + 128 * 160, "setmaxnreg budgets must add up to the launch allocation");
   std::lock_guard<std::mutex> lock(g_map_mu);
   MapEntry* set = g_maps + (map_hash(key) % kMapSets) * kMapWays;
   MapEntry* victim = set;
