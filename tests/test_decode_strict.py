@@ -136,6 +136,19 @@ def test_head_shard_rank_shapes_scale_aware(P, hkv):
     _check_with_negative_controls(P, q, kv, bts, lens, torch.bfloat16, peaked=True)
 
 
+@pytest.mark.timeout(180)
+def test_two_level_fold_uneven_partial_counts_complete_and_match(P):
+    """8 x 32k with 4 KV heads (the per-rank shape of head-sharded C3 at 2 GPUs): the guided split gives segments of
+    15, 16, 20, 24, 29 and 32 partials, i.e. two-level folds with ragged last groups, and one CTA can own several
+    groups of one segment.  An early round-2 kernel deadlocked exactly here (the final fold queued in front of a
+    group fold it polled for); the timeout turns a regression into a failure instead of a hung box.  Checked on every
+    sequence with peaked inputs, negative controls included, and bit-reproducible across two launches."""
+    q, kv, bts, lens = _case(8, [32768] * 8, 16, 4, 128, torch.bfloat16, seed=150, peaked=True)
+    out, _ = _check_with_negative_controls(P, q, kv, bts, lens, torch.bfloat16, rows=[0, 1, 2, 4, 5, 7], peaked=True)
+    again = P.paged_attention_decode_batched(q, kv, bts.to(DEV), lens.to(DEV))
+    assert torch.equal(out, again)
+
+
 def test_full_c2_batch_against_reference_row_by_row_arithmetic(P):
     """The whole 2048-token context of two C2 sequences against the reference's own bf16 row-by-row
     algorithm (oracle.decode_loop, bit-identical to paged_attention.py:80-101) - not a truncated prefix."""
