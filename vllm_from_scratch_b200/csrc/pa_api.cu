@@ -219,7 +219,7 @@ static int decode_impl(const void* q, int64_t q_stride_b, int64_t q_stride_h, vo
     p.q_tiles = (p.group + 7) / 8;
     // 16-byte aligned rows: the cp.async streaming kernel; anything else: the plain generic kernel
     stream_path = g_force_path.load() != 2 && pa_decode_stream_supported(p, cache->dtype);
-    p.num_workers = stream_path ? pa_decode_stream_workers(sms, &ctas) : pa_decode_generic_workers(sms, &ctas);
+    p.num_workers = stream_path ? pa_decode_stream_workers(p, cache->dtype, sms, &ctas) : pa_decode_generic_workers(sms, &ctas);
     slots = (int64_t)batch * Hkv * p.q_tiles + p.num_workers;
     rows = p.tile_q;
   }

@@ -176,7 +176,7 @@ int pa_decode_tma_header_ints();
 int pa_decode_tma_set_pdl(int on);
 int64_t pa_decode_tma_max_units(int batch, int num_kv_heads, int target_units);
 int pa_decode_generic_workers(int num_sms, int* ctas);
-int pa_decode_stream_workers(int num_sms, int* ctas);
+int pa_decode_stream_workers(const PaDecodeParams& p, int dtype, int num_sms, int* ctas);
 bool pa_decode_stream_supported(const PaDecodeParams& p, int dtype);
 int pa_launch_decode_stream(const PaDecodeParams& p, int dtype, int ctas, cudaStream_t stream);
 

@@ -17,12 +17,14 @@
 //          shared-memory tile so the PV phase reads them as broadcasts.
 //   PV   : lane <-> 16-byte column chunk of the V row, fp32 FMA.  m, l are lane-uniform.
 // fp32 FMA throughout (no tensor cores): an fp32 cache is read and multiplied at full precision.
+#include <type_traits>
+
 #include "pa_common.cuh"
 
 namespace {
 
 constexpr int kTQ = 8;              // query heads per head segment (same tile as pa_decode_generic.cu / pa_reduce.cu)
-constexpr int kWarpsS = 8;          // workers per CTA; one persistent CTA per SM
+constexpr int kWarpsS = 8;          // workers per CTA (16 where the registers allow: GQ = 4, one chunk per lane); one persistent CTA per SM
 constexpr int kMaxTS = 8;           // tokens per stage, at most
 constexpr int kSmemBudgetS = 227 * 1024;
 
@@ -51,23 +53,23 @@ struct StreamLayout {
   int ts, stages, stage_bytes;
 };
 // Shared-memory carve-up, identical on host and device.  stages < 2: the shape does not fit.
-__host__ __device__ inline StreamLayout stream_layout(int head_dim, int esize, int batch) {
+__host__ __device__ inline StreamLayout stream_layout(int head_dim, int esize, int batch, int warps, int gq) {
   StreamLayout L;
   const int row = head_dim * esize;
   int ts = kMaxTS;
-  while (ts > 1 && 2 * ts * row > 8192) ts >>= 1;
+  while (ts > 1 && 2 * ts * row > 65536 / warps) ts >>= 1;      // 8 KiB stages at 8 warps, 4 KiB at 16
   L.ts = ts;
   L.stage_bytes = 2 * ts * row;
   uint32_t o = 0;
-  L.q = o;        o += (uint32_t)kWarpsS * kTQ * head_dim * 4;
-  L.w = o;        o += kWarpsS * kMaxTS * kTQ * 4;
+  L.q = o;        o += (uint32_t)warps * gq * head_dim * 4;
+  L.w = o;        o += (uint32_t)warps * kMaxTS * gq * 4;
   L.scratch = o;  o += 40 * 4;
   L.cum = o;      o += (uint32_t)(batch + 1) * 4;
   o = (o + 15u) & ~15u;
   L.ring = o;
-  const int fit = ((int)kSmemBudgetS - (int)o - 16) / (kWarpsS * L.stage_bytes);
+  const int fit = ((int)kSmemBudgetS - (int)o - 16) / (warps * L.stage_bytes);
   L.stages = fit > 4 ? 4 : fit;
-  L.total = o + 16 + (uint32_t)(L.stages > 0 ? L.stages : 0) * kWarpsS * L.stage_bytes;
+  L.total = o + 16 + (uint32_t)(L.stages > 0 ? L.stages : 0) * warps * L.stage_bytes;
   return L;
 }
 
@@ -87,13 +89,15 @@ __device__ __forceinline__ void cp_wait(int pending) {     // at most `pending` 
 // T: cache / q / out element type.  CPL: 16-byte chunks of a V row per lane (head_dim <= 32 * CPL * N).
 // GQ: query heads computed per head segment (4 when the GQA group is <= 4, else the full tile of 8): the
 // kernel is bound by instruction issue at 8 warps per SM, so nothing is spent on predicated-off heads.
-template <typename T, int CPL, int GQ>
-__global__ void __launch_bounds__(kWarpsS * 32, 1)
+// WARPS: 8, or 16 with half-size stages (4 tokens: one token group) - the loop is bound by instruction issue and
+// fixed-latency stalls, and four warps per scheduler hide what two cannot; 16 x 32 threads leave 128 registers each.
+template <typename T, int CPL, int GQ, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1)
 pa_decode_stream_kernel(const PaDecodeParams p) {
   constexpr int N = Chunk<T>::N;
   extern __shared__ __align__(16) uint8_t smem_s[];
   const int D = p.head_dim, BS = p.block_size;
-  const StreamLayout L = stream_layout(D, (int)sizeof(T), p.batch);
+  const StreamLayout L = stream_layout(D, (int)sizeof(T), p.batch, WARPS, GQ);
   const int TS = L.ts, R = L.stages;
   const int row_bytes = D * (int)sizeof(T);
   const int cpr = row_bytes / 16;                      // 16-byte chunks per row
@@ -120,8 +124,8 @@ pa_decode_stream_kernel(const PaDecodeParams p) {
   const T* vbase = static_cast<const T*>(p.v);
   const T* qbase = static_cast<const T*>(p.q);
   T* obase = static_cast<T*>(p.out);
-  float* my_q = s_q + warp * kTQ * D;
-  float* my_w = reinterpret_cast<float*>(smem_s + L.w) + warp * kMaxTS * kTQ;
+  float* my_q = s_q + warp * GQ * D;
+  float* my_w = reinterpret_cast<float*>(smem_s + L.w) + warp * kMaxTS * GQ;
   const uint32_t ring_base = (static_cast<uint32_t>(__cvta_generic_to_shared(smem_s + L.ring)) + 15u) & ~15u;
   const uint32_t my_ring = ring_base + (uint32_t)warp * R * L.stage_bytes;
   const uint32_t my_w_s = static_cast<uint32_t>(__cvta_generic_to_shared(my_w));
@@ -205,37 +209,41 @@ pa_decode_stream_kernel(const PaDecodeParams p) {
 #pragma unroll
       for (int j = 0; j < GQ; ++j) sc[0][j] = sc[1][j] = 0.f;
       const bool v0 = tg < n, v1 = 4 + tg < n;
-      for (int c = q8; c < cpr; c += 8) {
-        float k0[N], k1[N];
+      auto qk = [&](auto ng_c) {
+        constexpr int NG = decltype(ng_c)::value;              // token groups of the stage: 2 (8 tokens) or 1 (<= 4)
+        for (int c = q8; c < cpr; c += 8) {
+          float k0[N], k1[N];
 #pragma unroll
-        for (int e = 0; e < N; ++e) k0[e] = k1[e] = 0.f;
-        if (v0) Chunk<T>::load(kst + (uint32_t)(tg * row_bytes + c * 16), k0);
-        if (v1) Chunk<T>::load(kst + (uint32_t)((4 + tg) * row_bytes + c * 16), k1);
+          for (int e = 0; e < N; ++e) k0[e] = k1[e] = 0.f;
+          if (v0) Chunk<T>::load(kst + (uint32_t)(tg * row_bytes + c * 16), k0);
+          if (NG == 2 && v1) Chunk<T>::load(kst + (uint32_t)((4 + tg) * row_bytes + c * 16), k1);
 #pragma unroll
-        for (int j = 0; j < GQ; ++j) {
+          for (int j = 0; j < GQ; ++j) {
 #pragma unroll
-          for (int e = 0; e < N; e += 4) {
-            float qv[4];
-            Chunk<float>::load(my_q_s + (uint32_t)((j * D + c * N + e) * 4), qv);
+            for (int e = 0; e < N; e += 4) {
+              float qv[4];
+              Chunk<float>::load(my_q_s + (uint32_t)((j * D + c * N + e) * 4), qv);
 #pragma unroll
-            for (int x = 0; x < 4; ++x) {
-              sc[0][j] = fmaf(k0[e + x], qv[x], sc[0][j]);
-              sc[1][j] = fmaf(k1[e + x], qv[x], sc[1][j]);
+              for (int x = 0; x < 4; ++x) {
+                sc[0][j] = fmaf(k0[e + x], qv[x], sc[0][j]);
+                if (NG == 2) sc[1][j] = fmaf(k1[e + x], qv[x], sc[1][j]);
+              }
             }
           }
         }
-      }
 #pragma unroll
-      for (int gi = 0; gi < 2; ++gi) {
+        for (int gi = 0; gi < NG; ++gi) {
 #pragma unroll
-        for (int j = 0; j < GQ; ++j) {
-          float v = sc[gi][j];
-          v += __shfl_xor_sync(0xffffffffu, v, 1);
-          v += __shfl_xor_sync(0xffffffffu, v, 2);
-          v += __shfl_xor_sync(0xffffffffu, v, 4);
-          sc[gi][j] = v;
+          for (int j = 0; j < GQ; ++j) {
+            float v = sc[gi][j];
+            v += __shfl_xor_sync(0xffffffffu, v, 1);
+            v += __shfl_xor_sync(0xffffffffu, v, 2);
+            v += __shfl_xor_sync(0xffffffffu, v, 4);
+            sc[gi][j] = v;
+          }
         }
-      }
+      };
+      if (TS > 4) qk(std::integral_constant<int, 2>{}); else qk(std::integral_constant<int, 1>{});
       // ---- online softmax over the stage -------------------------------------------------------
 #pragma unroll
       for (int j = 0; j < GQ; ++j) {
@@ -333,25 +341,41 @@ pa_decode_stream_kernel(const PaDecodeParams p) {
   }
 }
 
-template <typename T, int CPL, int GQ>
+template <typename T, int CPL, int GQ, int WARPS>
 int launch_s(const PaDecodeParams& p, int ctas, cudaStream_t stream) {
-  const StreamLayout L = stream_layout(p.head_dim, (int)sizeof(T), p.batch);
-  auto kern = pa_decode_stream_kernel<T, CPL, GQ>;
+  const StreamLayout L = stream_layout(p.head_dim, (int)sizeof(T), p.batch, WARPS, GQ);
+  auto kern = pa_decode_stream_kernel<T, CPL, GQ, WARPS>;
   static PaPerDeviceFlag attr;
   const int dev = attr.need();
   if (dev != -2) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBudgetS) != cudaSuccess) return -5;
     attr.done(dev);
   }
-  kern<<<ctas, kWarpsS * 32, L.total, stream>>>(p);
+  kern<<<ctas, WARPS * 32, L.total, stream>>>(p);
   return cudaGetLastError() == cudaSuccess ? 0 : -5;
 }
 
 }  // namespace
 
-int pa_decode_stream_workers(int num_sms, int* ctas) {
+// 16 warps where 128 registers per thread are enough (GQ = 4, one 16-byte chunk per lane) and a ring of >= 2
+// half-size stages fits; otherwise 8
+static int stream_warps(const PaDecodeParams& p, int dtype) {
+  const int esize = dtype == 1 ? 4 : 2;
+  // ... and only while a half-size stage still holds 8 tokens (rows <= 256 bytes: bf16 D <= 128, fp32 D <= 64): with
+  // 4-token stages the per-stage softmax and pipeline overhead eats the gain (fp32 D 128: 305 us against 285 us at
+  // 8 warps; bf16 D 128: 243 us against 300 us)
+  const StreamLayout L16 = stream_layout(p.head_dim, esize, p.batch, 16, 4);
+  const int wide = (p.group <= 4 && p.head_dim * esize / 16 <= 32 && L16.stages >= 2 && L16.ts == kMaxTS) ? 16 : kWarpsS;
+#ifdef PA_STREAM_WARPS
+  return PA_STREAM_WARPS == 16 ? wide : kWarpsS;
+#else
+  return wide;
+#endif
+}
+
+int pa_decode_stream_workers(const PaDecodeParams& p, int dtype, int num_sms, int* ctas) {
   *ctas = num_sms;
-  return num_sms * kWarpsS;
+  return num_sms * stream_warps(p, dtype);
 }
 
 // 16-byte aligned rows of whole 16-byte chunks, at most 32 * CPL chunks per row, and a ring of >= 2 stages
@@ -362,17 +386,20 @@ bool pa_decode_stream_supported(const PaDecodeParams& p, int dtype) {
   if ((p.kv_stride_block | p.kv_stride_head | p.kv_stride_slot) % n) return false;
   if (p.head_dim * esize / 16 > 64) return false;
   if (p.batch > PA_MAX_BATCH_SMEM) return false;
-  return stream_layout(p.head_dim, esize, p.batch).stages >= 2;
+  return stream_layout(p.head_dim, esize, p.batch, kWarpsS, p.group <= 4 ? 4 : 8).stages >= 2;
 }
 
 int pa_launch_decode_stream(const PaDecodeParams& p, int dtype, int ctas, cudaStream_t stream) {
   const int esize = dtype == 1 ? 4 : 2;
   const int cpr = p.head_dim * esize / 16;
   const bool g4 = p.group <= 4;               // every head segment has <= 4 live query heads
+  const bool w16 = stream_warps(p, dtype) == 16;
   if (dtype == 1) {
-    if (cpr <= 32) return g4 ? launch_s<float, 1, 4>(p, ctas, stream) : launch_s<float, 1, 8>(p, ctas, stream);
-    return g4 ? launch_s<float, 2, 4>(p, ctas, stream) : launch_s<float, 2, 8>(p, ctas, stream);
+    if (cpr <= 32) return g4 ? (w16 ? launch_s<float, 1, 4, 16>(p, ctas, stream) : launch_s<float, 1, 4, 8>(p, ctas, stream))
+                             : launch_s<float, 1, 8, 8>(p, ctas, stream);
+    return g4 ? launch_s<float, 2, 4, 8>(p, ctas, stream) : launch_s<float, 2, 8, 8>(p, ctas, stream);
   }
-  if (cpr <= 32) return g4 ? launch_s<__nv_bfloat16, 1, 4>(p, ctas, stream) : launch_s<__nv_bfloat16, 1, 8>(p, ctas, stream);
-  return g4 ? launch_s<__nv_bfloat16, 2, 4>(p, ctas, stream) : launch_s<__nv_bfloat16, 2, 8>(p, ctas, stream);
+  if (cpr <= 32) return g4 ? (w16 ? launch_s<__nv_bfloat16, 1, 4, 16>(p, ctas, stream) : launch_s<__nv_bfloat16, 1, 4, 8>(p, ctas, stream))
+                           : launch_s<__nv_bfloat16, 1, 8, 8>(p, ctas, stream);
+  return g4 ? launch_s<__nv_bfloat16, 2, 4, 8>(p, ctas, stream) : launch_s<__nv_bfloat16, 2, 8, 8>(p, ctas, stream);
 }
