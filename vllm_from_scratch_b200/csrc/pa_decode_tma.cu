@@ -391,9 +391,9 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       // The partial flag of this launch: epoch + 1, never 0 (a fresh workspace is all zeros).  Stable while any
       // CTA may still read it: only the LAST scheduler to finish advances it, and every scheduler reads it here.
       epoch = *reinterpret_cast<volatile int*>(ticket + 2);
-      scratch[kEpochSlot] = epoch + 1;
     }
     build_plan(p.seq_lens, p.batch, hs, p.target_units, p.guided_k * (int)gridDim.x, s_len, s_c, s_ucum, lane);
+    if (lane == 0) scratch[kEpochSlot] = epoch + 1;                    // (the load's round trip hid behind the plan)
     const int NU = s_ucum[p.batch] * hs;
     if (lane == 0) dbg_stamp(6);                                       // plan built
     // `nx_*`: the unit claimed next - located, with its first 64 block-table entries in registers.  A ticket is
