@@ -63,7 +63,7 @@ constexpr int kProducers = 8;       // TMA producer warps, one per consumer: war
 constexpr int kSchedWarp = kConsumers + kProducers;           // warp 16
 constexpr int kFinWarps = 3;        // finisher warps per CTA: warp 17 merges units, warps 18-19 fold split segments together
 constexpr int kFoldGroup = 8;       // segments of more partials are folded in two levels: groups of 8, then the groups
-constexpr int kJobRing = 32;        // fold jobs in flight merger -> folders (a CTA has a handful pending; see the merger)
+constexpr int kJobRing = 64;        // fold jobs in flight merger -> folders (a CTA has a handful pending; see the merger)
                                     //   (scheduler + finishers = one warpgroup)
 constexpr int kThreads = (kConsumers + kProducers + 1 + kFinWarps) * 32;   // 640
 constexpr int kDescRing = 8;        // unit descriptors in flight scheduler -> producers / consumers
