@@ -20,7 +20,7 @@
 //    at C2: of 84 us a consumer warp waited for KV data only 6 us, but spent 14 us stalled in the TMA
 //    issue path (back-pressure of a saturated memory system lands on whoever issues), 10 us in unit
 //    merges (~1 us per unit) and 24 us in the math.  So the roles are now separate:
-//      scheduler (warp 16): builds the plan, claims tickets one unit ahead, maps ticket -> (s, h, chunk)
+//      scheduler (warp 16): builds the plan, claims tickets, maps ticket -> (s, h, chunk)
 //        by binary search over the per-sequence unit prefix sums in shared memory, reads the unit's
 //        block-table entries with coalesced loads and publishes them, a unit descriptor and the unit's
 //        Q rows (cp.async.bulk) into a ring of 8 descriptor slots (full / empty mbarriers).
@@ -41,11 +41,17 @@
 //        GQA group; the kernel is bound by HBM, not by the tensor pipe.  At the end of a unit every
 //        consumer warp drops its (m, l, O) into a shared-memory hand-off area and goes straight on
 //        to the next unit - no CTA-wide barrier.
-//      finishers (warps 17-19): merge the 8 warps' states of the unit; a unit that covers its whole
-//        segment is normalised and written to `out`, otherwise the merged partial goes to the
-//        workspace (coalesced, 2 KiB at g = 4) and the unit is checked in at the segment's atomic
-//        counter; for the last unit of a segment to arrive they merge the segment's partials and write
-//        `out` - no second launch, and the consumers never wait for a global-memory round trip.
+//      merger (warp 17): merges the 8 warps' states of a unit and frees the hand-off area at once; a unit that
+//        covers its whole segment is normalised and written to `out`, otherwise the merged partial goes to the
+//        workspace as self-validating 16-byte words {value, epoch, value, epoch} (plain stores, no fence) and,
+//        for the unit that owns the fold (a segment's first unit; for > 8 partials the first unit of every
+//        group of 8, the last group's also for the final fold), a fold job is posted to the folders.
+//      folders (warps 18-19): fold a split segment's partials in chunk order, half of the GQA heads each, 4
+//        partials' loads in flight per lane, polling one sentinel word per partial until the batch has landed,
+//        and write `out` - no second launch, no atomic and no fence on the hand-over, and the consumers never
+//        wait for a global-memory round trip.
+//      (scheduler: a ticket is claimed only when the CTA's backlog is short, and a unit is published in
+//       16-block descriptors - see the scheduler branch; register budgets per role via setmaxnreg.)
 //  * results are bit-reproducible: the block -> warp assignment and every merge order depend only
 //    on the batch shape, never on which SM took which unit.
 #include <atomic>
