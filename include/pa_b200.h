@@ -85,7 +85,8 @@ int pa_decode_num_workers(void);
  * units, followed by a cross-partition merge.
  * Two launches on the generic path (fp32 caches, odd shapes); ONE on the fast
  * path (bf16, block_size 16, head_dim 64 / 128, g <= 8), whose kernel merges
- * its own split-K partials ("the last unit of a segment to arrive merges").
+ * its own split-K partials (the CTA that ran a split segment's first unit folds
+ * them, polling self-validating words: no second launch, no atomic, no fence).
  * workspace: pa_decode_workspace_bytes() bytes, 16-byte aligned, owned by the
  *   caller.  Its first 1 MiB is a counter header that must be ZERO on entry:
  *   call pa_decode_workspace_init once after allocating it (or memset it);

@@ -39,11 +39,11 @@ int pa_decode_set_tuning(int units_per_sm, int guided_k, int stages, int claim_l
  * one stream overlap the next kernel's prologue with the previous kernel's tail.  Returns the old setting. */
 int pa_decode_set_pdl(int on);
 /* Debug: when non-null, every fast-path CTA writes its timeline, 16 int64 at device_buffer[16 * cta]
- * (globaltimer ns): [0] SM id, [1] CTA start, [2] consumers' end, [3] units processed, [4] finishers'
+ * (globaltimer ns): [0] SM id, [1] CTA start, [2] consumers' end, [3] units processed, [4] merger / folders'
  * end, [5] first KV block landed, [6] plan built, [7] first unit published, [8] first TMA load issued,
  * [9] ticket counter found exhausted, [10] last unit merged, [11] last fold job taken by the folders, [12] its last
  * batch of partials seen; (SM cycles, consumer warp 0:) [13] waited for unit descriptors,
- * [14] for KV data, [15] for the hand-off area to the finishers.  pa_decode_num_workers() entries.   */
+ * [14] for KV data, [15] for the hand-off area to the merger.  pa_decode_num_workers() entries.   */
 int pa_decode_debug_times(void* device_buffer);
 /* Same for the tcgen05 prefill kernel: 8 int64 per CTA (grid order x, y, z): SM id,
  * globaltimer at entry / prologue done / Q stored / first S / O complete / outputs
