@@ -582,8 +582,9 @@ def install(engine: Any, ops: Any = None, cuda_graphs: Optional[bool] = None) ->
     tc = False
     if tc_fn is not None and device.type == "cuda":
         tc = bool(tc_fn((engine.model.k_cache[0], engine.model.v_cache[0]), a0.num_heads))
+    # capacities start at the scheduler's own limits (tokens capped: the staging grows on demand)
     tables = StepTables(device, ops, block_size, getattr(sched, "max_num_seqs", 16),
-                        getattr(sched, "max_num_batched_tokens", 256), 64,
+                        min(int(getattr(sched, "max_num_batched_tokens", 256)), 8192), 64,
                         token_tables=not tc and hasattr(ops, "paged_attention_decode_batched"))
     state = {"ops": ops, "meta": None, "orig_schedule": sched.schedule, "tables": tables, "workspace": None,
              "workspace_cap": 0, "orig_forwards": [layer.attn.forward for layer in layers], "graphs": None,
