@@ -321,7 +321,7 @@ namespace {
 // Receiver side of the LL gather: every 8-byte word {data, flag} that a remote rank stored into this
 // rank's LL area is polled until its flag equals this step's number, and its data word is written
 // into the gather set.  The last block to finish advances the step number.  Bounded like the wait.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 pa_peer_unpack_kernel(const uint2* ll, uint32_t* gathered, int world, int rank, int words, uint32_t* epoch,
                       uint32_t* done, unsigned long long timeout_ns, int32_t* status) {
   const uint32_t flag = *reinterpret_cast<volatile uint32_t*>(epoch) + 1u;
@@ -347,6 +347,13 @@ pa_peer_unpack_kernel(const uint2* ll, uint32_t* gathered, int world, int rank, 
     }
     gathered[i] = v.x;
   }
+  // The kernel is launched with programmatic stream serialisation right behind pa_decode_gather (which lets its
+  // dependents go at its very start): these small CTAs (128 threads, no shared memory) fit next to a decode CTA, so
+  // the polling above overlaps the local decode instead of starting after it.  Nothing above depends on the local
+  // decode (its own slot is skipped); everything below does - the step number may only advance once the local
+  // kernel, which stamps its outgoing words with it, has finished, and the consumers behind this kernel on the
+  // stream need the local slot complete as well.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
@@ -366,12 +373,20 @@ extern "C" int pa_peer_unpack(const void* ll_local, void* gathered, int32_t worl
   if ((reinterpret_cast<uintptr_t>(ll_local) & 7) || (reinterpret_cast<uintptr_t>(gathered) & 3)) return PA_ERR_MISALIGNED;
   const int64_t total = (int64_t)world * words_per_slot;
   if (total > 0x7fffffff) return PA_ERR_UNSUPPORTED;
-  int blocks = (int)((total + 256 * 8 - 1) / (256 * 8));   // ~8 words per thread
-  if (blocks > 64) blocks = 64;
-  pa_peer_unpack_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const uint2*>(ll_local), static_cast<uint32_t*>(gathered), world, rank, words_per_slot, epoch, done,
-      (unsigned long long)timeout_us * 1000ull, status);
-  return cudaGetLastError() == cudaSuccess ? PA_OK : PA_ERR_CUDA;
+  int blocks = (int)((total + 128 * 8 - 1) / (128 * 8));   // ~8 words per thread
+  if (blocks > 128) blocks = 128;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(blocks);
+  cfg.blockDim = dim3(128);
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, pa_peer_unpack_kernel, static_cast<const uint2*>(ll_local), static_cast<uint32_t*>(gathered),
+                            (int)world, (int)rank, (int)words_per_slot, epoch, done,
+                            (unsigned long long)timeout_us * 1000ull, status) == cudaSuccess ? PA_OK : PA_ERR_CUDA;
 }
 
 extern "C" int pa_peer_alloc(size_t bytes, void** ptr, void* ipc_handle_64) {
