@@ -164,7 +164,10 @@ int pa_peer_wait_next(const uint32_t* local_sig, int32_t world, uint32_t* epoch,
  * data words into `gathered` ([world][words_per_slot] uint32; the local slot is
  * left alone - the decode kernel wrote it in place), then advances *epoch.
  * `done` is a zero-initialised device word (block counter).  Bounded like
- * pa_peer_wait.  Graph-capturable (no per-step host argument).                */
+ * pa_peer_wait.  Graph-capturable (no per-step host argument).  Launched with
+ * programmatic stream serialisation: behind pa_decode_gather its CTAs poll the
+ * incoming words while the local decode kernel is still running, and only its
+ * tail (step number, completion) waits for that kernel.                        */
 int pa_peer_unpack(const void* ll_local, void* gathered, int32_t world, int32_t rank,
                    int32_t words_per_slot, uint32_t* epoch, uint32_t* done,
                    int64_t timeout_us, int32_t* status, void* stream);
