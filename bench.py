@@ -43,6 +43,8 @@ WORKLOADS = {
            "C3 long-context decode: 8 seqs x 32768 ctx, GQA 32/8, head_dim 128, bf16, block_size 16"),
     "c5": (64, 8192, 32, 8, 128, 16, 2,
            "C5 shard: 64 seqs x 8192 ctx per GPU (512 seqs over 8 GPUs), GQA 32/8, head_dim 128, bf16"),
+    "c2d64": (64, 4096, 32, 8, 64, 16, 8,
+              "C2-sized decode at head_dim 64: 64 seqs x 4096 ctx, 32 Q / 8 KV heads, bf16 (experiments only)"),
     "c3r8": (8, 32768, 4, 1, 128, 16, 4,
              "per-rank shape of KV-head-sharded C3 at 8 GPUs: 8 seqs x 32768 ctx, 4 Q / 1 KV head (experiments only)"),
     "c5h": (64, 32768, 32, 8, 128, 16, 2,

@@ -78,7 +78,7 @@ constexpr int kNumBars = 2 * kConsumers * 8 /* kMaxStages */ + 3 * kDescRing + 2
 #define PA_DESC_BLOCKS 16
 #endif
 #ifndef PA_FOLD_DEPTH
-#define PA_FOLD_DEPTH (HD == 128 ? 4 : 2)
+#define PA_FOLD_DEPTH 4
 #endif
 constexpr int kDescBlocks = PA_DESC_BLOCKS;   // blocks per descriptor (a unit spans several); a multiple of 8, 16 / 32 / 64
 constexpr int kMaxStages = 8;       // per-warp ring depth cap (kNumBars assumes 8)
@@ -449,7 +449,8 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
     // published blocks are unconsumed: deep enough to keep the 8 x R stage rings full, shallow enough that the
     // release of one descriptor is a fine-grained progress signal.  The next ticket is claimed when the backlog
     // (outstanding + unpublished rest of the current unit) drops below claim_limit + kDescBlocks.
-    const int pub_cap = p.claim_limit, claim_at = p.claim_limit + kDescBlocks;
+    // claim_limit is quoted in 8-KiB blocks (head_dim 128); a head_dim-64 block is half the bytes
+    const int pub_cap = p.claim_limit * (128 / HD), claim_at = pub_cap + kDescBlocks;
     int cs = 0, ch = 0, b0 = 0, n = 0, nch = 0, t = 0, c = 0, bt0 = 0, bt1 = 0, j0 = 0, last_valid = kBS;
     bool have_cur = false, next_ready = true;                        // the first unit is already in nx_*
     for (;;) {
@@ -644,7 +645,7 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
         }
       }
     } else {
-      constexpr int FU = 4;                                       // rows (value words per lane) of one pass
+      constexpr int FU = 2 * IPH;                                 // rows (value words per lane) of one pass: two heads
       constexpr int HPG = FU / IPH;                               // heads of one pass
       constexpr int DEPTH = PA_FOLD_DEPTH;                    // partials in flight per lane: DEPTH * (FU + HPG) words
       const int h0 = fw == 1 ? 0 : (g + 1) / 2, h1 = fw == 1 ? (g + 1) / 2 : g;   // this folder's GQA heads
