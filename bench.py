@@ -43,6 +43,14 @@ WORKLOADS = {
            "C3 long-context decode: 8 seqs x 32768 ctx, GQA 32/8, head_dim 128, bf16, block_size 16"),
     "c5": (64, 8192, 32, 8, 128, 16, 2,
            "C5 shard: 64 seqs x 8192 ctx per GPU (512 seqs over 8 GPUs), GQA 32/8, head_dim 128, bf16"),
+    # shape scan (experiments only; same KV byte count as C2 unless noted)
+    "x_mha": (16, 2048, 32, 32, 128, 16, 4, "MHA: 16 seqs x 2048 ctx, 32 Q / 32 KV heads"),
+    "x_g8": (64, 2048, 64, 8, 128, 16, 4, "GQA 8: 64 seqs x 2048 ctx, 64 Q / 8 KV heads"),
+    "x_b1": (1, 131072, 32, 8, 128, 16, 4, "one sequence of 131072 tokens"),
+    "x_b512": (512, 256, 32, 8, 128, 16, 4, "512 seqs x 256 ctx"),
+    "x_b4": (4, 4096, 32, 8, 128, 16, 4, "4 seqs x 4096 ctx (32 MiB of KV)"),
+    "x_b1s": (1, 2048, 32, 8, 128, 16, 4, "1 seq x 2048 ctx (4 MiB of KV)"),
+    "x_b8": (8, 1024, 32, 8, 128, 16, 4, "8 seqs x 1024 ctx (16 MiB of KV)"),
     "c2d64": (64, 4096, 32, 8, 64, 16, 8,
               "C2-sized decode at head_dim 64: 64 seqs x 4096 ctx, 32 Q / 8 KV heads, bf16 (experiments only)"),
     "c3r8": (8, 32768, 4, 1, 128, 16, 4,

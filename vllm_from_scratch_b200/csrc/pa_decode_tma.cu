@@ -68,6 +68,7 @@ constexpr int kConsumers = 8;       // consumer (math) warps per CTA: warps 0-7,
 constexpr int kProducers = 8;       // TMA producer warps, one per consumer: warps 8-15
 constexpr int kSchedWarp = kConsumers + kProducers;           // warp 16
 constexpr int kFinWarps = 3;        // finisher warps per CTA: warp 17 merges units, warps 18-19 fold split segments together
+constexpr int kMinUnitBlocks = 32;  // smallest split-K unit, in 8-KiB blocks (head_dim 128; twice as many blocks at head_dim 64)
 constexpr int kFoldGroup = 8;       // segments of more partials are folded in two levels: groups of 8, then the groups
 constexpr int kJobRing = 64;        // fold jobs in flight merger -> folders (a CTA has a handful pending; see the merger)
                                     //   (scheduler + finishers = one warpgroup)
@@ -246,7 +247,7 @@ __device__ __forceinline__ int warp_scan_inplace(int* a, int n, int lane) {
 // the uniform size that yields target_units units.  C(s) is a multiple of 8: every consumer warp
 // gets the same share of a full unit.  Outputs: s_len[s] = max(seq_len, 0), s_c[s] = C(s),
 // s_ucum = exclusive scan of ceil(nblk(s) / C(s)) (s_ucum[batch] = units per KV head).
-__device__ __forceinline__ void build_plan(const int32_t* __restrict__ seq_lens, int batch, int hs, int target_units,
+__device__ __forceinline__ void build_plan(const int32_t* __restrict__ seq_lens, int batch, int hs, int target_units, int min_unit,
                                            int guided_div, int* s_len, int* s_c, int* s_ucum, int lane) {
   for (int i = lane; i < batch; i += 32) {
     const int len = max(__ldg(seq_lens + i), 0);
@@ -255,7 +256,10 @@ __device__ __forceinline__ void build_plan(const int32_t* __restrict__ seq_lens,
   }
   __syncwarp();
   const int total = warp_scan_inplace(s_c, batch, lane) * hs;             // s_c[s] = blocks before sequence s
-  const int c_min = 8 * max(1, pa_ceil_div(total, 8 * target_units));
+  // never below kMinUnitBlocks (256 KiB at head_dim 128): on small batches (tens of MiB of KV) finer units buy no
+  // balance worth their folds - 4 x 4096 tokens took 38 us in 8-block units (32 partials per segment, a 15 us fold
+  // backlog after 24 us of streaming)
+  const int c_min = max(8 * max(1, pa_ceil_div(total, 8 * target_units)), min_unit);
   for (int i = lane; i < batch; i += 32) {
     const int nblk = pa_ceil_div(s_len[i], kBS);
     const int remaining = total - s_c[i] * hs;
@@ -398,7 +402,8 @@ pa_decode_ws_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_const
       // CTA may still read it: only the LAST scheduler to finish advances it, and every scheduler reads it here.
       epoch = *reinterpret_cast<volatile int*>(ticket + 2);
     }
-    build_plan(p.seq_lens, p.batch, hs, p.target_units, p.guided_k * (int)gridDim.x, s_len, s_c, s_ucum, lane);
+    build_plan(p.seq_lens, p.batch, hs, p.target_units, kMinUnitBlocks * (128 / HD), p.guided_k * (int)gridDim.x, s_len, s_c,
+               s_ucum, lane);
     if (lane == 0) scratch[kEpochSlot] = epoch + 1;                    // (the load's round trip hid behind the plan)
     const int NU = s_ucum[p.batch] * hs;
     if (lane == 0) dbg_stamp(6);                                       // plan built
