@@ -42,7 +42,9 @@ typedef enum PaStatus {
   PA_ERR_MISALIGNED = -3,   /* pointer or stride alignment requirement not met   */
   PA_ERR_WORKSPACE = -4,    /* workspace too small                                */
   PA_ERR_CUDA = -5,         /* a CUDA runtime / driver call failed                */
-  PA_ERR_NO_DEVICE = -6     /* no sm_100 device is current                        */
+  PA_ERR_NO_DEVICE = -6,    /* no sm_100 device is current                        */
+  PA_ERR_STATIC_LIMIT = -7  /* pa_decode_static: the shape needs more scratch than
+                             * PA_DECODE_STATIC_BYTES; use pa_decode + a workspace */
 } PaStatus;
 
 typedef enum PaDtype { PA_BF16 = 0, PA_F32 = 1 } PaDtype;
@@ -105,6 +107,33 @@ int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h,
               int32_t batch, int32_t num_q_heads,
               void* workspace, size_t workspace_bytes,
               void* stream /* cudaStream_t */);
+
+/* ---- decode without a workspace, for callers that may not allocate -------
+ * No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph
+ * capture, tight serving loops, harnesses that forbid it).  Same arguments,
+ * kernels and results as pa_decode (bit-identical outputs); the workspace is a
+ * file-scope device array of PA_DECODE_STATIC_BYTES inside the library, held by
+ * every GPU that loads the library until the process exits.  The call, and
+ * everything it reaches, calls no cudaMalloc / cudaFree / allocating routine.
+ * Limit: a shape whose pa_decode_workspace_bytes() exceeds
+ *   PA_DECODE_STATIC_BYTES returns PA_ERR_STATIC_LIMIT and launches nothing
+ *   (96 MiB holds e.g. batch <= 256 at 32 query / 8 KV heads of dim 128; the
+ *   need grows with batch * num_q_heads * head_dim) - use pa_decode then.
+ * Sharing: ALL calls on a device use the same array, which keeps the previous
+ *   call's contents (the kernels leave their counters at zero and stamp partials
+ *   with a per-launch epoch, so nothing needs clearing between calls).  Calls
+ *   that can overlap on the GPU - different streams without an ordering event -
+ *   RACE on it: keep them on one stream, or use pa_decode with one workspace
+ *   per stream.                                                               */
+#define PA_DECODE_STATIC_BYTES (96u << 20)
+int pa_decode_static(const void* q, int64_t q_stride_b, int64_t q_stride_h,
+                     void* out, int64_t o_stride_b, int64_t o_stride_h,
+                     const PaKvCache* cache,
+                     const int32_t* block_tables, int32_t bt_stride,
+                     const int32_t* seq_lens,
+                     int32_t batch, int32_t num_q_heads,
+                     void* stream /* cudaStream_t */);
 
 /* ---- decode fused with the output gather of KV-head-sharded decode ---------
  * (rank r owns KV heads [r Hkv/P, (r+1) Hkv/P) of every

@@ -53,6 +53,9 @@ SIGNATURES = {
     "pa_decode_workspace_init": (c_int, [c_void_p, c_size_t, c_void_p]),
     "pa_decode": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
                           c_void_p, c_int32, c_void_p, c_int32, c_int32, c_void_p, c_size_t, c_void_p]),
+    # no workspace argument: the library's static device array (PA_DECODE_STATIC_BYTES), see include/pa_b200.h
+    "pa_decode_static": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
+                                 c_void_p, c_int32, c_void_p, c_int32, c_int32, c_void_p]),
     "pa_decode_gather": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, POINTER(PaKvCache),
                                  c_void_p, c_int32, c_void_p, c_int32, c_int32, c_void_p, c_size_t,
                                  POINTER(PaPeerGather), c_void_p]),

@@ -20,7 +20,7 @@ INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 BUILD = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libpa_b200.so")
 
-SOURCES = ["pa_api.cu", "pa_decode_tma.cu", "pa_decode_generic.cu", "pa_decode_stream.cu", "pa_reduce.cu", "pa_cache_ops.cu", "pa_prefill_tc.cu", "pa_prefill_tc2.cu", "pa_rope_cache.cu"]
+SOURCES = ["pa_api.cu", "pa_decode_tma.cu", "pa_decode_generic.cu", "pa_decode_stream.cu", "pa_decode_static.cu", "pa_reduce.cu", "pa_cache_ops.cu", "pa_prefill_tc.cu", "pa_prefill_tc2.cu", "pa_rope_cache.cu"]
 HEADERS = [os.path.join(CSRC, "pa_common.cuh"), os.path.join(CSRC, "pa_tc_common.cuh"), os.path.join(INCLUDE, "pa_b200.h"), os.path.join(INCLUDE, "pa_b200_debug.h")]
 
 NVCC_FLAGS = [

@@ -95,6 +95,7 @@ extern "C" const char* pa_status_string(int status) {
     case PA_ERR_WORKSPACE: return "workspace too small";
     case PA_ERR_CUDA: return "CUDA call failed";
     case PA_ERR_NO_DEVICE: return "no sm_100 device is current";
+    case PA_ERR_STATIC_LIMIT: return "shape needs more scratch than the static array of pa_decode_static holds";
     default: return "unknown status";
   }
 }
