@@ -668,7 +668,19 @@ def run_ours(args):
             torch.cuda.current_stream().synchronize()
 
     ne2e -= ne2e % 2 if peer_mode else 0
+    # Untimed ramp of this leg: building and capturing the steps above left the GPU idle for tens of ms, and a
+    # step here keeps it only ~75 % busy, so the clocks take a few hundred ms of steps to come back
+    # (tools/exp_e2e_jitter.py: 177 us per step for the first ~0.3 s, 116 us from then on - every step, not
+    # outliers).  Six steps to size the ramp, then --ramp-ms worth of steps; the count is agreed over ranks
+    # (the multi-GPU legs hold collectives / peer hand-shakes).
+    t_w = time.perf_counter()
     for i in range(6):
+        e2e_step(i)
+    torch.cuda.synchronize()
+    per = max((time.perf_counter() - t_w) / 6, 1e-6)
+    n_ramp = int(timer.max_over_ranks([min(args.ramp_ms * 1e-3 / per, 10000.0)], dev)[0])
+    n_ramp += n_ramp % 2
+    for i in range(n_ramp):
         e2e_step(i)
     ms_e2e, _, _ = timer.run(e2e_step, ne2e, lead=0)
     sampler.stop_flag.set()
@@ -709,7 +721,7 @@ def run_ours(args):
                      "algorithmic_bytes_per_launch": kv_bytes + io_bytes,
                      "frac_of_nominal_8tbs": achieved / NOMINAL_HBM_GBS, "launches_timed": args.steps},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": ne2e, "ms_per_step": ms_e2e / ne2e,
+                "steps": ne2e, "warmup": 6 + n_ramp, "ms_per_step": ms_e2e / ne2e,
                 "what": "graph.DecodeStep: every input of the step starts in pinned host memory; new K / V rows, "
                         "slots, block tables and seq lens cross PCIe as one staged H2D copy, the decode kernel reads "
                         "q from and writes out to pinned host memory in place (zero-copy over PCIe; both counted in "
