@@ -25,6 +25,7 @@
 //     maximum grew by more than 2^8 over the maximum in use (exact: l and O share that reference).
 // TMEM (512 columns): S_A / P_A [0,128) | S_B / P_B [128,256) | O_A [256,384) | O_B [384,512).
 // Shared memory (D = 128): Q_A, Q_B 32 KiB each | ring 5 x 32 KiB = 224 KiB.
+#include <atomic>
 #include <cuda.h>
 #include <math.h>
 #include <stdio.h>
@@ -50,6 +51,15 @@ constexpr uint32_t kTmemO = 256;
 constexpr float kRescaleThreshold = 8.f;      // log2 units
 constexpr uint32_t FULL = 0xffffffffu;
 
+// Work tiles published ahead of the slowest reader.  ONE, and drawn as late as possible (when the producer has
+// two K / V tiles of the current work tile left to request): list scheduling is only as good as the moment a
+// ticket is drawn.  Measured on full8k: ring of 4 filled at start-up 998 TFLOP/s (every CTA draws its tickets in
+// the first microsecond - the list is dealt out before any work is done); ring of 1 refilled as soon as it is
+// read 1083 (a CTA that starts a 45-tile unit has already committed to the one after it); a static
+// boustrophedon deal 1121.
+constexpr int kTileRing = 1;
+constexpr int kDrawAhead = 2;                 // K / V tiles of the current work tile still to be requested when the next ticket is drawn
+
 // Barrier slots (8 bytes each).  Per-warpgroup groups are indexed [wg].
 enum : int {
   kBarKvFull = 0, kBarKvEmpty = kRing,
@@ -57,8 +67,19 @@ enum : int {
   kBarPReady = kBarSFull + 2,       // [wg][2]  128 softmax threads: keys [0,64) / [64,128) of P(t) are in TMEM (and O is rescaled)
   kBarODone = kBarPReady + 4,       // [wg]  tcgen05.commit after the warpgroup's last P V
   kBarQReady = kBarODone + 2,       // [wg]  128 softmax threads: the Q tile is in shared memory
-  kNumBars = kBarQReady + 2
+  kBarTFull = kBarQReady + 2,       // [kTileRing]  the scheduler warp published a work tile
+  kBarTEmpty = kBarTFull + kTileRing,   // [kTileRing]  every reader (2 x 128 softmax threads, producer, issuer) has taken it
+  kBarTReq = kBarTEmpty + kTileRing,    // the producer is about to run out of K / V tiles to request: draw the next work tile
+  kNumBars = kBarTReq + 1
 };
+constexpr int kTileReaders = 2 * kWgThreads + 2;
+
+// Work-tile tickets of the launches in flight: [slot][0] = next work tile of the launch, [1] = CTAs that have run
+// out of tiles.  Zero when the module is loaded; the last CTA of a launch to run out puts its slot back to zero.
+// A launch takes slot (launch number % kTicketSlots): two launches share a slot only if kTicketSlots launches
+// apart AND running at the same time.
+constexpr int kTicketSlots = 1024;
+__device__ int g_tickets[kTicketSlots * 2];
 
 // D[tmem] (+)= A[tmem] . B[smem]
 __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
@@ -126,36 +147,57 @@ constexpr int kTraceTiles = 48, kTraceSlots = 16;
     if (trace_on && (t) < kTraceTiles) p.trace[(t) * kTraceSlots + (slot)] = clock64();           \
   } while (0)
 
+// One unit of work: 2 * R tokens (tile A = the first R, tile B = the rest) of one (sequence, KV head).
+struct WorkTile {
+  int s, h, q_start, tok0, ntok_a, ntok_b, pos0, n_a, n_b, n, nblk_need, ctx;
+  int slot;                                                  // index in the debug stamp buffer (the old 3-D grid's linear block index)
+};
+// Work tile number L of the launch, longest tiles first: the query tile index is the slowest axis (a later
+// query tile attends to more keys), (sequence, KV head) the fastest.  false = nothing to do there.
+__device__ __forceinline__ bool work_tile(const PaPrefillParams& p, int L, int gx, int R, WorkTile& T) {
+  const int per_x = p.num_kv_heads * p.batch;
+  const int x = L / per_x, rem = L - x * per_x;
+  T.s = rem / p.num_kv_heads;
+  T.h = rem - T.s * p.num_kv_heads;
+  T.slot = x + gx * (T.h + p.num_kv_heads * T.s);
+  int q_len;
+  if (p.cu_q_lens) {
+    T.q_start = __ldg(p.cu_q_lens + T.s);
+    q_len = __ldg(p.cu_q_lens + T.s + 1) - T.q_start;
+    T.ctx = __ldg(p.ctx_lens + T.s);
+  } else {
+    T.q_start = 0; q_len = p.num_tokens; T.ctx = p.ctx_len_single;
+  }
+  if (q_len <= 0 || T.ctx < q_len) return false;             // nothing to do / malformed: leave `out` alone
+  T.tok0 = (gx - 1 - x) * 2 * R;
+  if (T.tok0 >= q_len) return false;
+  const int ntok = min(2 * R, q_len - T.tok0);
+  T.ntok_a = min(R, ntok);
+  T.ntok_b = ntok - T.ntok_a;
+  T.pos0 = T.ctx - q_len + T.tok0;                           // smallest query position of the tile
+  T.n_a = (T.pos0 + T.ntok_a - 1) / kTileN + 1;
+  T.n_b = T.ntok_b > 0 ? (T.pos0 + ntok - 1) / kTileN + 1 : 0;
+  T.n = max(T.n_a, T.n_b);                                   // KV tiles streamed
+  T.nblk_need = (T.pos0 + ntok - 1) / kBS + 1;
+  if (p.max_blocks > 0 && pa_ceil_div(T.ctx, kBS) > p.max_blocks) return false;   // the table row is too short: never read past it
+  return true;
+}
+
+// Persistent: one CTA per SM.  Warp 10 draws work tiles from the launch's ticket (the list is sorted longest first,
+// so this is longest-processing-time-first list scheduling), drops the empty ones and publishes the rest through a
+// small shared-memory ring that the four other roles read in the same order.  Barriers, TMEM and the register
+// split are set up once; barrier phases run on across tiles (each role counts its own waits), the K / V ring never
+// drains: the producer is already fetching the next tile's keys while the softmax warpgroups write the current
+// tile's output, and a warpgroup stages its next Q tile before it waits for its last P V.
 template <int HD>
 __global__ void __launch_bounds__(kThreads, 1)
 pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
-                      const PaPrefillParams p) {
+                      const PaPrefillParams p, const int gx, const int total_tiles, const int ticket_slot) {
   constexpr int HALVES = HD / 64;
   constexpr uint32_t kItem = HALVES * kSlab;                 // one Q, K or V tile: [half][128 rows][128 B]
 
-  // ---- which work tile: 2 * R tokens of one (sequence, KV head) ----
-  const int s = blockIdx.z, h = blockIdx.y;
   const int g = p.group, R = kRows / g;
-  int q_start, q_len, ctx;
-  if (p.cu_q_lens) {
-    q_start = __ldg(p.cu_q_lens + s);
-    q_len = __ldg(p.cu_q_lens + s + 1) - q_start;
-    ctx = __ldg(p.ctx_lens + s);
-  } else {
-    q_start = 0; q_len = p.num_tokens; ctx = p.ctx_len_single;
-  }
-  if (q_len <= 0 || ctx < q_len) return;                     // nothing to do / malformed: leave `out` alone
-  const int cta_tile = (int)gridDim.x - 1 - (int)blockIdx.x; // long tiles first
-  const int tok0 = cta_tile * 2 * R;
-  if (tok0 >= q_len) return;
-  const int ntok_cta = min(2 * R, q_len - tok0);
-  const int ntok_a = min(R, ntok_cta), ntok_b = ntok_cta - ntok_a;
-  const int pos0 = ctx - q_len + tok0;                       // smallest query position of the CTA
-  const int n_a = (pos0 + ntok_a - 1) / kTileN + 1;
-  const int n_b = ntok_b > 0 ? (pos0 + ntok_cta - 1) / kTileN + 1 : 0;
-  const int n = max(n_a, n_b);                               // KV tiles the CTA streams
-  const int nblk_need = (pos0 + ntok_cta - 1) / kBS + 1;
-  if (p.max_blocks > 0 && pa_ceil_div(ctx, kBS) > p.max_blocks) return;   // the table row is too short: never read past it
+  const int cta = (int)blockIdx.x;
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -163,38 +205,39 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
   const uint32_t sRing = sQ + 2 * kItem;
   const uint32_t sBar = sRing + kRing * kItem;
   const uint32_t sTmem = sBar + kNumBars * 8;
+  const uint32_t sTiles = sTmem + 16;                        // [kTileRing] published work tiles (-1: no more)
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));     // generic pointer to `base`
   auto bar = [&](int i) { return sBar + 8u * i; };
+  // the cnt-th work tile of this CTA (every reader calls this once per tile, in order); -1 = the CTA is done
+  auto next_tile = [&](int& cnt) {
+    const int e = cnt % kTileRing;
+    mbar_wait(bar(kBarTFull + e), (cnt / kTileRing) & 1);
+    int L;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(L) : "r"(sTiles + 4u * e) : "memory");
+    mbar_arrive(bar(kBarTEmpty + e));
+    ++cnt;
+    return L;
+  };
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const bool trace_on = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (tid & 127) == 0;
+  const bool trace_cta = p.trace != nullptr && cta == 0;     // stamps of this CTA's FIRST work tile only
 
-  // debug: per-CTA wall-clock stamps (thread 0): [0] smid [1] entry [2] prologue done [3] Q stored
+  // debug: per-work-tile wall-clock stamps (thread 0): [0] smid [1] entry [2] prologue done [3] Q stored
   // [4] first S ready [5] O complete [6] outputs stored [7] KV tiles streamed
-  long long* const ct = (p.cta_times != nullptr && tid == 0)
-                            ? p.cta_times + 8 * ((int64_t)blockIdx.x + (int64_t)gridDim.x * (blockIdx.y + (int64_t)gridDim.y * blockIdx.z))
-                            : nullptr;
-  auto stamp = [&](int slot) {
-    if (ct) {
+  auto stamp_at = [&](int slot_index, int slot) {
+    if (p.cta_times != nullptr && (tid & 127) == 0) {
       unsigned long long t;
       asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-      ct[slot] = (long long)t;
+      p.cta_times[8 * (int64_t)slot_index + slot] = (long long)t;
     }
   };
-  if (ct) {
-    unsigned smid;
-    asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
-    ct[0] = smid;
-    ct[7] = n;
-  }
-  stamp(1);
 
   if (warp == 8 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_k) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_v) : "memory");
     for (int i = 0; i < kNumBars; ++i) {
-      const bool by_warpgroup = (i >= kBarPReady && i < kBarODone) || i >= kBarQReady;
-      mbar_init(bar(i), by_warpgroup ? kWgThreads : 1);
+      const bool by_warpgroup = (i >= kBarPReady && i < kBarODone) || (i >= kBarQReady && i < kBarTFull);
+      mbar_init(bar(i), (i >= kBarTEmpty && i < kBarTReq) ? kTileReaders : by_warpgroup ? kWgThreads : 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -207,61 +250,104 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gen + (sTmem - base));
-  stamp(2);
 
   if (warp < 8) {
     // =============================== softmax warpgroups ===============================
     asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");    // from 168: the 128 x 128 registers the third warpgroup gives up cover 64 x 256
     const int w = warp >> 2;                                 // 0 = tile A, 1 = tile B
     const int wt = tid & (kWgThreads - 1);                   // row within the tile = TMEM lane
-    const int ntok_w = w == 0 ? ntok_a : ntok_b;
-    const int n_w = w == 0 ? n_a : n_b;
-    if (ntok_w > 0) {
-      const int tokw0 = tok0 + w * R, posw0 = pos0 + w * R;
-      // ---- Q tile -> shared memory, K-major, 128-byte swizzle (row = (token, head-in-group)) ----
-      {
-        const __nv_bfloat16* qb = static_cast<const __nv_bfloat16*>(p.q);
-        constexpr int CH = HD / 8;                           // 16-byte chunks per row
-        uint8_t* qdst = gen + (sQ - base) + (uint32_t)w * kItem;
-        // all loads first, then all stores: as one load -> store per iteration the loop ran at one global
-        // round trip per iteration (measured 9.3 us per CTA, more than four KV tiles of work)
-        constexpr int ITERS = kRows * CH / kWgThreads;       // 16 (D 128) / 8 (D 64)
-        uint4 val[ITERS];
-#pragma unroll
-        for (int it = 0; it < ITERS; ++it) {
-          const int idx = wt + it * kWgThreads;
-          const int row = idx / CH, c = idx % CH;
-          const int ti = row / g, j = row - ti * g;
-          val[it] = make_uint4(0, 0, 0, 0);
-          if (ti < ntok_w)
-            val[it] = __ldg(reinterpret_cast<const uint4*>(qb + (int64_t)(q_start + tokw0 + ti) * p.q_stride_t +
-                                                           (int64_t)(h * g + j) * p.q_stride_h + c * 8));
-        }
-#pragma unroll
-        for (int it = 0; it < ITERS; ++it) {
-          const int idx = wt + it * kWgThreads;
-          const int row = idx / CH, c = idx % CH;
-          const uint32_t off = (uint32_t)(c >> 3) * kSlab + (uint32_t)row * 128u + (uint32_t)(((c & 7) ^ (row & 7)) << 4);
-          *reinterpret_cast<uint4*>(qdst + off) = val[it];
-        }
-        fence_proxy_async();
-        mbar_arrive(bar(kBarQReady + w));
-        stamp(3);
+    const float scale = p.scale_log2e;
+    const uint64_t scale2 = pack2(scale, scale);
+    const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    const uint32_t tS = lane_base + (uint32_t)w * 128u, tO = lane_base + kTmemO + (uint32_t)w * 128u;
+    const int ti = wt / g, j = wt - ti * g;
+
+    // The warpgroup's own walk over the CTA's work tiles: `item0` = ring items (K / V tiles) the CTA streamed
+    // before the current work tile - every valid tile counts, also those this warpgroup has no rows in.
+    // Only the tile's index L and its ring position live across the KV loop; whatever else a phase needs is
+    // derived from L again (a few cached loads) - 232 registers hold a row of 128 scores and little else.
+    int t_cnt = 0, item0_next = 0;
+    int L_cur = -1, item0 = 0;
+    auto advance = [&](int& into_L, int& into_item0) -> bool {      // next work tile with rows for this warpgroup
+      for (;;) {
+        const int L = next_tile(t_cnt);
+        if (L < 0) return false;
+        WorkTile c;
+        if (!work_tile(p, L, gx, R, c)) continue;
+        const int at = item0_next;
+        item0_next += 2 * c.n;
+        if ((w == 0 ? c.ntok_a : c.ntok_b) > 0) { into_L = L; into_item0 = at; return true; }
       }
-      const int ti = wt / g, j = wt - ti * g;
-      const bool valid = ti < ntok_w;
-      const int qpos = posw0 + min(ti, ntok_w - 1);
-      const float scale = p.scale_log2e;
-      const uint64_t scale2 = pack2(scale, scale);
-      const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-      const uint32_t tS = lane_base + (uint32_t)w * 128u, tO = lane_base + kTmemO + (uint32_t)w * 128u;
+    };
+    // ---- Q tile -> shared memory, K-major, 128-byte swizzle (row = (token, head-in-group)) ----
+    auto stage_q = [&](const int L) {
+      WorkTile c;
+      work_tile(p, L, gx, R, c);
+      const int ntok_w = w == 0 ? c.ntok_a : c.ntok_b;
+      const int tokw0 = c.tok0 + w * R;
+      const __nv_bfloat16* qb = static_cast<const __nv_bfloat16*>(p.q);
+      constexpr int CH = HD / 8;                             // 16-byte chunks per row
+      uint8_t* qdst = gen + (sQ - base) + (uint32_t)w * kItem;
+      // all loads first, then all stores: as one load -> store per iteration the loop ran at one global
+      // round trip per iteration (measured 9.3 us per CTA, more than four KV tiles of work)
+      constexpr int ITERS = kRows * CH / kWgThreads;         // 16 (D 128) / 8 (D 64)
+      uint4 val[ITERS];
+#pragma unroll
+      for (int it = 0; it < ITERS; ++it) {
+        const int idx = wt + it * kWgThreads;
+        const int row = idx / CH, c8 = idx % CH;
+        const int rti = row / g, rj = row - rti * g;
+        val[it] = make_uint4(0, 0, 0, 0);
+        if (rti < ntok_w)
+          val[it] = __ldg(reinterpret_cast<const uint4*>(qb + (int64_t)(c.q_start + tokw0 + rti) * p.q_stride_t +
+                                                         (int64_t)(c.h * g + rj) * p.q_stride_h + c8 * 8));
+      }
+#pragma unroll
+      for (int it = 0; it < ITERS; ++it) {
+        const int idx = wt + it * kWgThreads;
+        const int row = idx / CH, c8 = idx % CH;
+        const uint32_t off = (uint32_t)(c8 >> 3) * kSlab + (uint32_t)row * 128u + (uint32_t)(((c8 & 7) ^ (row & 7)) << 4);
+        *reinterpret_cast<uint4*>(qdst + off) = val[it];
+      }
+      fence_proxy_async();
+      mbar_arrive(bar(kBarQReady + w));
+      if (w == 0) stamp_at(c.slot, 3);
+    };
+
+    int s_cnt = 0, o_cnt = 0;                                // S tiles / work tiles this warpgroup has waited for so far
+    bool have = advance(L_cur, item0);
+    if (have) stage_q(L_cur);
+    bool first_tile = true;
+    while (have) {
+      int n_w, n, posw0, qpos, slot;
+      bool valid;
+      {
+        WorkTile T;
+        work_tile(p, L_cur, gx, R, T);
+        const int ntok_w = w == 0 ? T.ntok_a : T.ntok_b;
+        n_w = w == 0 ? T.n_a : T.n_b;
+        n = T.n;
+        posw0 = T.pos0 + w * R;
+        valid = ti < ntok_w;
+        qpos = posw0 + min(ti, ntok_w - 1);
+        slot = T.slot;
+        if (w == 0 && p.cta_times != nullptr && wt == 0) {
+          unsigned smid;
+          asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+          p.cta_times[8 * (int64_t)slot] = smid;
+          p.cta_times[8 * (int64_t)slot + 7] = n;
+        }
+        if (w == 0) { stamp_at(slot, 1); stamp_at(slot, 2); }
+      }
+      const bool trace_on = trace_cta && first_tile && (tid & 127) == 0;
       float m_used = -INFINITY, l = 0.f;
 
       for (int t = 0; t < n_w; ++t) {
         uint32_t v[kTileN];
         // S(t) complete; the commit behind this barrier also covers P V(t - 1): O holds tiles < t
-        mbar_wait(bar(kBarSFull + w), t & 1);
-        if (t == 0) stamp(4);
+        mbar_wait(bar(kBarSFull + w), s_cnt & 1);
+        ++s_cnt;
+        if (t == 0 && w == 0) stamp_at(slot, 4);
         PA_TRACE(5 * w + 0, t);
         tc_fence_after();
         // the scores arrive in two halves: the row maximum of keys [0, 64) is taken while keys [64, 128)
@@ -319,11 +405,13 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
             tmem_st32(tO + cc * 32, o);
           }
         }
-        // ---- the CTA's last tile: V rows that were not loaded or lie beyond the context must be finite ----
+        // ---- the work tile's last KV tile: V rows that were not loaded or lie beyond the context must be finite ----
         if (t == n - 1) {
-          const int zero_from = min(nblk_need * kBS, ctx) - kbase;
+          WorkTile T;
+          work_tile(p, L_cur, gx, R, T);
+          const int zero_from = min(T.nblk_need * kBS, T.ctx) - kbase;
           if (zero_from < kTileN) {
-            const int item = 2 * t + 1;
+            const int item = item0 + 2 * t + 1;
             mbar_wait(bar(kBarKvFull + item % kRing), (item / kRing) & 1);
             const int nz = (kTileN - zero_from) * HALVES * 8;
             uint8_t* vb = gen + (sRing - base) + (uint32_t)(item % kRing) * kItem;
@@ -369,13 +457,25 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
         l = l * alpha + (s0 + s1);
       }
 
+      // ---- the next work tile's Q goes to shared memory now: every Q K^T of this one is complete (the last S
+      // was waited for above), and the loads run while the pipe finishes this tile's last P V ----
+      int L_n = -1, item0_n = 0;
+      const bool have_n = advance(L_n, item0_n);
+      if (have_n) stage_q(L_n);
+
       // ---- epilogue: O / l -> out ----
-      mbar_wait(bar(kBarODone + w), 0);
-      stamp(5);
+      mbar_wait(bar(kBarODone + w), o_cnt & 1);
+      ++o_cnt;
+      if (w == 0) stamp_at(slot, 5);
       tc_fence_after();
       const float inv = 1.f / l;
-      __nv_bfloat16* ob = static_cast<__nv_bfloat16*>(p.out) + (int64_t)(q_start + tokw0 + ti) * p.o_stride_t +
-                          (int64_t)(h * g + j) * p.o_stride_h;
+      __nv_bfloat16* ob;
+      {
+        WorkTile T;
+        work_tile(p, L_cur, gx, R, T);
+        ob = static_cast<__nv_bfloat16*>(p.out) + (int64_t)(T.q_start + T.tok0 + w * R + ti) * p.o_stride_t +
+             (int64_t)(T.h * g + j) * p.o_stride_h;
+      }
 #pragma unroll
       for (int cc = 0; cc < HD / 32; ++cc) {
         uint32_t o[32];
@@ -393,32 +493,49 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
           }
         }
       }
-      stamp(6);
+      if (w == 0) stamp_at(slot, 6);
+      // O is read: the next tile's first P V may overwrite it.  That MMA is issued behind this warpgroup's
+      // next P-ready arrival, which every thread makes after this point.
       tc_fence_before();
+      L_cur = L_n;
+      item0 = item0_n;
+      have = have_n;
+      first_tile = false;
     }
   }
   else {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
   if (warp == 8) {
     // =============================== TMA producer ===============================
-    const int32_t* bt = p.block_tables + (int64_t)s * p.bt_stride;
     const int b = lane / HALVES, hf = lane % HALVES;
-    for (int t = 0; t < n; ++t) {
-      const int blk0 = t * kBlocksPerTile;
-      const int nb = min(kBlocksPerTile, nblk_need - blk0);
-      const bool mine = lane < kBlocksPerTile * HALVES && b < nb;
-      int blk = 0;
-      if (mine) blk = __ldg(bt + blk0 + b);
-      const int c3 = p.pos_head == 3 ? h : blk, c4 = p.pos_head == 3 ? blk : h;
-      const uint32_t in_item = (uint32_t)hf * kSlab + (uint32_t)b * (kBS * 128);
+    int item0 = 0, t_cnt = 0;
+    for (;;) {
+      int L = 0;
+      if (lane == 0) L = next_tile(t_cnt);
+      L = __shfl_sync(FULL, L, 0);
+      if (L < 0) break;
+      WorkTile T;
+      if (!work_tile(p, L, gx, R, T)) continue;
+      const int32_t* bt = p.block_tables + (int64_t)T.s * p.bt_stride;
+      for (int t = 0; t < T.n; ++t) {
+        if (t == max(T.n - 1 - kDrawAhead, 0) && lane == 0) mbar_arrive(bar(kBarTReq));
+        const int blk0 = t * kBlocksPerTile;
+        const int nb = min(kBlocksPerTile, T.nblk_need - blk0);
+        const bool mine = lane < kBlocksPerTile * HALVES && b < nb;
+        int blk = 0;
+        if (mine) blk = __ldg(bt + blk0 + b);
+        const int c3 = p.pos_head == 3 ? T.h : blk, c4 = p.pos_head == 3 ? blk : T.h;
+        const uint32_t in_item = (uint32_t)hf * kSlab + (uint32_t)b * (kBS * 128);
 #pragma unroll
-      for (int kv = 0; kv < 2; ++kv) {                       // item 2t = K(t), item 2t + 1 = V(t)
-        const int item = 2 * t + kv, slot = item % kRing;
-        mbar_wait(bar(kBarKvEmpty + slot), ((item / kRing) & 1) ^ 1);
-        if (lane == 0) mbar_expect_tx(bar(kBarKvFull + slot), (uint32_t)nb * HALVES * kBS * 128);
-        __syncwarp();
-        if (mine) tma_load_half(sRing + (uint32_t)slot * kItem + in_item, kv ? &tm_v : &tm_k, bar(kBarKvFull + slot), hf, c3, c4);
+        for (int kv = 0; kv < 2; ++kv) {                     // item 2t = K(t), item 2t + 1 = V(t)
+          const int item = item0 + 2 * t + kv, slot = item % kRing;
+          mbar_wait(bar(kBarKvEmpty + slot), ((item / kRing) & 1) ^ 1);
+          if (lane == 0) mbar_expect_tx(bar(kBarKvFull + slot), (uint32_t)nb * HALVES * kBS * 128);
+          __syncwarp();
+          if (mine) tma_load_half(sRing + (uint32_t)slot * kItem + in_item, kv ? &tm_v : &tm_k, bar(kBarKvFull + slot), hf, c3, c4);
+        }
       }
+      item0 += 2 * T.n;
     }
   } else if (warp == 9) {
     // =============================== MMA issuer ===============================
@@ -429,13 +546,15 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
       constexpr uint32_t idesc_o = umma_idesc(HD, true);
       constexpr uint64_t kDescK = ((uint64_t)(16 >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
       constexpr uint64_t kDescV = ((uint64_t)(kSlab >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
-      const bool tr = p.trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+      int item0 = 0;
+      uint32_t ph = 0;                                       // phase bits: 0, 1 = Q ready of A / B; 2, 3 = P ready of A / B
+      bool tr = trace_cta;                                   // first work tile of CTA 0 only
       auto wait_item = [&](int item) { mbar_wait(bar(kBarKvFull + item % kRing), (item / kRing) & 1); };
       auto free_item = [&](int item) { umma_commit(bar(kBarKvEmpty + item % kRing)); };
       auto qk = [&](int w, int t) {                          // S_w = Q_w K(t)^T   (both operands in shared memory)
         if (tr && t < kTraceTiles) p.trace[t * kTraceSlots + 11 + 2 * w] = clock64();
         const uint64_t da = kDescK | (uint64_t)(((sQ + (uint32_t)w * kItem) & 0x3FFFFu) >> 4);
-        const uint64_t db = kDescK | (uint64_t)(((sRing + (uint32_t)((2 * t) % kRing) * kItem) & 0x3FFFFu) >> 4);
+        const uint64_t db = kDescK | (uint64_t)(((sRing + (uint32_t)((item0 + 2 * t) % kRing) * kItem) & 0x3FFFFu) >> 4);
         const uint32_t d = tmem + (uint32_t)w * 128u;
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
@@ -446,42 +565,112 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
       };
       auto pv = [&](int w, int t, bool last) {               // O_w += P_w V(t)      (P in TMEM, V in shared memory)
         // the first 64 keys' P V runs while the warpgroup still exponentiates the other 64
-        mbar_wait(bar(kBarPReady + 2 * w), t & 1);
+        const uint32_t par = (ph >> (2 + w)) & 1u;
+        ph ^= 4u << w;
+        mbar_wait(bar(kBarPReady + 2 * w), par);
         if (tr && t < kTraceTiles) p.trace[t * kTraceSlots + 10 + 2 * w] = clock64();
         tc_fence_after();
-        const uint64_t db = kDescV | (uint64_t)(((sRing + (uint32_t)((2 * t + 1) % kRing) * kItem) & 0x3FFFFu) >> 4);
+        const uint64_t db = kDescV | (uint64_t)(((sRing + (uint32_t)((item0 + 2 * t + 1) % kRing) * kItem) & 0x3FFFFu) >> 4);
         const uint32_t d = tmem + kTmemO + (uint32_t)w * 128u, a = tmem + (uint32_t)w * 128u;
         umma_bf16_ts(d, a, db, idesc_o, t > 0 ? 1u : 0u);
 #pragma unroll
         for (int ks = 1; ks < kTileN / 32; ++ks) umma_bf16_ts(d, a + (uint32_t)ks * 8u, db + (uint64_t)(ks * (16 * 128 >> 4)), idesc_o, 1u);
-        mbar_wait(bar(kBarPReady + 2 * w + 1), t & 1);
+        mbar_wait(bar(kBarPReady + 2 * w + 1), par);
         tc_fence_after();
 #pragma unroll
         for (int ks = kTileN / 32; ks < kTileN / 16; ++ks) umma_bf16_ts(d, a + (uint32_t)ks * 8u, db + (uint64_t)(ks * (16 * 128 >> 4)), idesc_o, 1u);
         if (last) umma_commit(bar(kBarODone + w));
       };
-      mbar_wait(bar(kBarQReady), 0);
-      if (ntok_b > 0) mbar_wait(bar(kBarQReady + 1), 0);
-      tc_fence_after();
-      wait_item(0);
-      qk(0, 0);
-      if (n_b > 0) qk(1, 0);
-      free_item(0);
-      for (int t = 0; t < n; ++t) {
-        wait_item(2 * t + 1);                                // V(t)
-        if (t + 1 < n) wait_item(2 * t + 2);                 // K(t + 1)
-        if (t < n_a) {
-          pv(0, t, t == n_a - 1);
-          if (t + 1 < n_a) qk(0, t + 1);
+      int t_cnt = 0;
+      for (;;) {
+        const int L = next_tile(t_cnt);
+        if (L < 0) break;
+        WorkTile T;
+        if (!work_tile(p, L, gx, R, T)) continue;
+        const int n = T.n, n_a = T.n_a, n_b = T.n_b;
+        mbar_wait(bar(kBarQReady), ph & 1u);
+        ph ^= 1u;
+        if (T.ntok_b > 0) {
+          mbar_wait(bar(kBarQReady + 1), (ph >> 1) & 1u);
+          ph ^= 2u;
         }
-        if (t < n_b) {
-          pv(1, t, t == n_b - 1);
-          if (t + 1 < n_b) qk(1, t + 1);
+        tc_fence_after();
+        wait_item(item0);
+        qk(0, 0);
+        if (n_b > 0) qk(1, 0);
+        free_item(item0);
+        for (int t = 0; t < n; ++t) {
+          wait_item(item0 + 2 * t + 1);                      // V(t)
+          if (t + 1 < n) wait_item(item0 + 2 * t + 2);       // K(t + 1)
+          if (t < n_a) {
+            pv(0, t, t == n_a - 1);
+            if (t + 1 < n_a) qk(0, t + 1);
+          }
+          if (t < n_b) {
+            pv(1, t, t == n_b - 1);
+            if (t + 1 < n_b) qk(1, t + 1);
+          }
+          free_item(item0 + 2 * t + 1);
+          if (t + 1 < n) free_item(item0 + 2 * t + 2);
         }
-        free_item(2 * t + 1);
-        if (t + 1 < n) free_item(2 * t + 2);
+        item0 += 2 * n;
+        tr = false;
       }
       tc_fence_before();
+    }
+    __syncwarp();
+  } else if (warp == 10) {
+    // =============================== work-tile scheduler ===============================
+    int* const tk = g_tickets + 2 * ticket_slot;
+    int pub = 0;
+    auto publish = [&](int L) {                              // lane 0
+      const int e = pub % kTileRing;
+      mbar_wait(bar(kBarTEmpty + e), ((pub / kTileRing) & 1) ^ 1);
+      asm volatile("st.shared.b32 [%0], %1;" ::"r"(sTiles + 4u * e), "r"(L) : "memory");
+      mbar_arrive(bar(kBarTFull + e));
+      ++pub;
+    };
+    const int hkv = p.num_kv_heads, pairs = total_tiles / hkv;   // a (query tile, sequence) pair = hkv consecutive tickets, all empty or none
+    int drawn = 0;                                           // tickets with work published so far
+    for (;;) {
+      // the first draw is immediate, every later one waits for the producer's request
+      if (drawn > 0 && lane == 0) mbar_wait(bar(kBarTReq), (drawn - 1) & 1);
+      __syncwarp();
+      int L = 0;
+      if (lane == 0) L = atomicAdd(tk, 1);
+      L = __shfl_sync(FULL, L, 0);
+      if (L >= total_tiles) break;
+      WorkTile T;
+      if (work_tile(p, L, gx, R, T)) {
+        if (lane == 0) publish(L);
+        ++drawn;
+        continue;
+      }
+      // An empty tile (a sequence shorter than the launch's longest, a masked row): the 32 lanes look for the
+      // next pair that has work and move the launch's ticket there in one step - whoever gets there first.
+      int pair = L / hkv + 1, found = pairs;
+      while (pair < pairs) {
+        bool v = false;
+        if (pair + lane < pairs) {
+          WorkTile U;
+          v = work_tile(p, (pair + lane) * hkv, gx, R, U);
+        }
+        const unsigned m = __ballot_sync(FULL, v);
+        if (m) {
+          found = pair + __ffs(m) - 1;
+          break;
+        }
+        pair += 32;
+      }
+      if (lane == 0) atomicMax(tk, found * hkv);
+    }
+    if (lane == 0) {
+      publish(-1);
+      // every CTA draws exactly one ticket past the end, after its last touch of the slot: the last to do so clears it
+      if (atomicAdd(tk + 1, 1) == (int)gridDim.x - 1) {
+        tk[0] = 0;
+        tk[1] = 0;
+      }
     }
     __syncwarp();
   }
@@ -496,7 +685,18 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
 
 template <int HD>
 constexpr size_t smem_bytes() {
-  return 1024 + (size_t)(HD / 64) * kSlab * (2 + kRing) + kNumBars * 8 + 16;
+  return 1024 + (size_t)(HD / 64) * kSlab * (2 + kRing) + kNumBars * 8 + 16 + kTileRing * 4;
+}
+
+int sm_count_cached() {
+  static int cached[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return -1; }
+  if (dev >= 0 && dev < 64 && cached[dev] > 0) return cached[dev];
+  int n = 0;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) { cudaGetLastError(); return -1; }
+  if (dev >= 0 && dev < 64) cached[dev] = n;
+  return n;
 }
 
 template <int HD>
@@ -510,8 +710,16 @@ int launch(const PaPrefillParams& p, const CUtensorMap& mk, const CUtensorMap& m
     attr.done(dev);
   }
   const int R2 = 2 * (kRows / p.group);
-  dim3 grid((p.max_q_len + R2 - 1) / R2, p.num_kv_heads, p.batch);
-  kern<<<grid, kThreads, smem_bytes<HD>(), stream>>>(mk, mv, p);
+  const int gx = (p.max_q_len + R2 - 1) / R2;
+  const int64_t total = (int64_t)gx * p.num_kv_heads * p.batch;
+  if (total <= 0) return 0;
+  if (total > 0x7fffffff) return -2;
+  const int sms = sm_count_cached();
+  if (sms <= 0) return -5;
+  const int ctas = (int)(total < sms ? total : sms);          // persistent: one CTA per SM walks the work tiles
+  static std::atomic<unsigned> launches{0};
+  const int slot = (int)(launches.fetch_add(1) % (unsigned)kTicketSlots);
+  kern<<<ctas, kThreads, smem_bytes<HD>(), stream>>>(mk, mv, p, gx, (int)total, slot);
   return cudaGetLastError() == cudaSuccess ? 0 : -5;
 }
 
