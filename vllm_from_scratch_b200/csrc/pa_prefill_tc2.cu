@@ -268,55 +268,65 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
     // derived from L again (a few cached loads) - 232 registers hold a row of 128 scores and little else.
     int t_cnt = 0, item0_next = 0;
     int L_cur = -1, item0 = 0;
+    // The CTA's next work tile: 1 = it has rows for this warpgroup, 0 = it has none (tile B of a short tail), -1 = no
+    // more tiles.  Reads exactly one entry of the ring: the entry after a tile is published while that tile is still
+    // being worked on, the one after THAT only once the tile is nearly done - a warpgroup in the middle of a tile
+    // must never wait for it (the issuer would wait for the warpgroup, the producer for the issuer).
+    auto advance_one = [&](int& into_L, int& into_item0) -> int {
+      const int L = next_tile(t_cnt);
+      if (L < 0) return -1;
+      WorkTile c;
+      if (!work_tile(p, L, gx, R, c)) return 0;
+      const int at = item0_next;
+      item0_next += 2 * c.n;
+      if ((w == 0 ? c.ntok_a : c.ntok_b) == 0) return 0;
+      into_L = L;
+      into_item0 = at;
+      return 1;
+    };
     auto advance = [&](int& into_L, int& into_item0) -> bool {      // next work tile with rows for this warpgroup
       for (;;) {
-        const int L = next_tile(t_cnt);
-        if (L < 0) return false;
-        WorkTile c;
-        if (!work_tile(p, L, gx, R, c)) continue;
-        const int at = item0_next;
-        item0_next += 2 * c.n;
-        if ((w == 0 ? c.ntok_a : c.ntok_b) > 0) { into_L = L; into_item0 = at; return true; }
+        const int r = advance_one(into_L, into_item0);
+        if (r != 0) return r > 0;
       }
     };
     // ---- Q tile -> shared memory, K-major, 128-byte swizzle (row = (token, head-in-group)) ----
-    auto stage_q = [&](const int L) {
+    // Asynchronous copies (cp.async, 16 bytes each, rows past the tile's tokens zero-filled): nothing passes through
+    // registers, so the copies of the NEXT work tile's Q are issued at the top of the current tile's last softmax
+    // pass - every Q K^T of the tile has completed by then - and their global round trip is over when it ends.
+    auto stage_q_issue = [&](const int L) {
       WorkTile c;
       work_tile(p, L, gx, R, c);
       const int ntok_w = w == 0 ? c.ntok_a : c.ntok_b;
       const int tokw0 = c.tok0 + w * R;
       const __nv_bfloat16* qb = static_cast<const __nv_bfloat16*>(p.q);
       constexpr int CH = HD / 8;                             // 16-byte chunks per row
-      uint8_t* qdst = gen + (sQ - base) + (uint32_t)w * kItem;
-      // all loads first, then all stores: as one load -> store per iteration the loop ran at one global
-      // round trip per iteration (measured 9.3 us per CTA, more than four KV tiles of work)
+      const uint32_t qdst = sQ + (uint32_t)w * kItem;
       constexpr int ITERS = kRows * CH / kWgThreads;         // 16 (D 128) / 8 (D 64)
-      uint4 val[ITERS];
 #pragma unroll
       for (int it = 0; it < ITERS; ++it) {
         const int idx = wt + it * kWgThreads;
         const int row = idx / CH, c8 = idx % CH;
         const int rti = row / g, rj = row - rti * g;
-        val[it] = make_uint4(0, 0, 0, 0);
-        if (rti < ntok_w)
-          val[it] = __ldg(reinterpret_cast<const uint4*>(qb + (int64_t)(c.q_start + tokw0 + rti) * p.q_stride_t +
-                                                         (int64_t)(c.h * g + rj) * p.q_stride_h + c8 * 8));
-      }
-#pragma unroll
-      for (int it = 0; it < ITERS; ++it) {
-        const int idx = wt + it * kWgThreads;
-        const int row = idx / CH, c8 = idx % CH;
+        const bool live = rti < ntok_w;
+        const __nv_bfloat16* src = qb + (int64_t)(c.q_start + tokw0 + (live ? rti : 0)) * p.q_stride_t +
+                                   (int64_t)(c.h * g + rj) * p.q_stride_h + c8 * 8;
         const uint32_t off = (uint32_t)(c8 >> 3) * kSlab + (uint32_t)row * 128u + (uint32_t)(((c8 & 7) ^ (row & 7)) << 4);
-        *reinterpret_cast<uint4*>(qdst + off) = val[it];
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(qdst + off), "l"(src), "r"(live ? 16 : 0) : "memory");
       }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      return c.slot;
+    };
+    auto stage_q_commit = [&](const int slot_of) {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
       fence_proxy_async();
       mbar_arrive(bar(kBarQReady + w));
-      if (w == 0) stamp_at(c.slot, 3);
+      if (w == 0) stamp_at(slot_of, 3);
     };
 
     int s_cnt = 0, o_cnt = 0;                                // S tiles / work tiles this warpgroup has waited for so far
     bool have = advance(L_cur, item0);
-    if (have) stage_q(L_cur);
+    if (have) stage_q_commit(stage_q_issue(L_cur));
     bool first_tile = true;
     while (have) {
       int n_w, n, posw0, qpos, slot;
@@ -341,6 +351,7 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
       }
       const bool trace_on = trace_cta && first_tile && (tid & 127) == 0;
       float m_used = -INFINITY, l = 0.f;
+      int L_n = -1, item0_n = 0, slot_n = 0, next_state = 0;
 
       for (int t = 0; t < n_w; ++t) {
         uint32_t v[kTileN];
@@ -350,6 +361,10 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
         if (t == 0 && w == 0) stamp_at(slot, 4);
         PA_TRACE(5 * w + 0, t);
         tc_fence_after();
+        if (t == n_w - 1) {                                  // the tile's last S: its Q tile is not read any more
+          next_state = advance_one(L_n, item0_n);
+          if (next_state > 0) slot_n = stage_q_issue(L_n);
+        }
         // the scores arrive in two halves: the row maximum of keys [0, 64) is taken while keys [64, 128)
         // are still on their way from TMEM (tiles that need the causal / ragged mask wait for both first)
         tmem_ld32(tS, v);
@@ -457,11 +472,9 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
         l = l * alpha + (s0 + s1);
       }
 
-      // ---- the next work tile's Q goes to shared memory now: every Q K^T of this one is complete (the last S
-      // was waited for above), and the loads run while the pipe finishes this tile's last P V ----
-      int L_n = -1, item0_n = 0;
-      const bool have_n = advance(L_n, item0_n);
-      if (have_n) stage_q(L_n);
+      // ---- the next work tile's Q is in shared memory: the issuer may start its first Q K^T behind this tile's
+      // last P V, while this warpgroup writes the tile's output ----
+      if (next_state > 0) stage_q_commit(slot_n);
 
       // ---- epilogue: O / l -> out ----
       mbar_wait(bar(kBarODone + w), o_cnt & 1);
@@ -497,6 +510,11 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
       // O is read: the next tile's first P V may overwrite it.  That MMA is issued behind this warpgroup's
       // next P-ready arrival, which every thread makes after this point.
       tc_fence_before();
+      bool have_n = next_state > 0;
+      if (next_state == 0) {                                 // the next tile had no rows for this warpgroup: now it may wait
+        have_n = advance(L_n, item0_n);
+        if (have_n) stage_q_commit(stage_q_issue(L_n));
+      }
       L_cur = L_n;
       item0 = item0_n;
       have = have_n;
