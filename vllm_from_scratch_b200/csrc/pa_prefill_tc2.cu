@@ -51,13 +51,13 @@ constexpr uint32_t kTmemO = 256;
 constexpr float kRescaleThreshold = 8.f;      // log2 units
 constexpr uint32_t FULL = 0xffffffffu;
 
-// Work tiles published ahead of the slowest reader.  ONE, and drawn as late as possible (when the producer has
+// Work tiles published ahead of the slowest reader: ONE, and drawn as late as possible (when the producer has
 // two K / V tiles of the current work tile left to request): list scheduling is only as good as the moment a
 // ticket is drawn.  Measured on full8k: ring of 4 filled at start-up 998 TFLOP/s (every CTA draws its tickets in
 // the first microsecond - the list is dealt out before any work is done); ring of 1 refilled as soon as it is
 // read 1083 (a CTA that starts a 45-tile unit has already committed to the one after it); a static
 // boustrophedon deal 1121.
-constexpr int kTileRing = 1;
+constexpr int kTileRing = 2;                  // entries: the tile being worked on and the next (an entry is released when its tile is DONE)
 constexpr int kDrawAhead = 2;                 // K / V tiles of the current work tile still to be requested when the next ticket is drawn
 
 // Barrier slots (8 bytes each).  Per-warpgroup groups are indexed [wg].
@@ -148,10 +148,16 @@ constexpr int kTraceTiles = 48, kTraceSlots = 16;
   } while (0)
 
 // One unit of work: 2 * R tokens (tile A = the first R, tile B = the rest) of one (sequence, KV head).
-struct WorkTile {
-  int s, h, q_start, tok0, ntok_a, ntok_b, pos0, n_a, n_b, n, nblk_need, ctx;
+struct __align__(16) WorkTile {                              // 16 ints: published through shared memory as four 16-byte words
+  int s, h, q_start, tok0;
+  int ntok_a, ntok_b, pos0, n_a;
+  int n_b, n, nblk_need, ctx;
   int slot;                                                  // index in the debug stamp buffer (the old 3-D grid's linear block index)
+  int item0;                                                 // K / V ring items the CTA streamed before this tile
+  int L;                                                     // index in the launch's list; -1 = the CTA has no more tiles
+  int pad;
 };
+static_assert(sizeof(WorkTile) == 64, "four 16-byte words");
 // Work tile number L of the launch, longest tiles first: the query tile index is the slowest axis (a later
 // query tile attends to more keys), (sequence, KV head) the fastest.  false = nothing to do there.
 __device__ __forceinline__ bool work_tile(const PaPrefillParams& p, int L, int gx, int R, WorkTile& T) {
@@ -205,19 +211,26 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
   const uint32_t sRing = sQ + 2 * kItem;
   const uint32_t sBar = sRing + kRing * kItem;
   const uint32_t sTmem = sBar + kNumBars * 8;
-  const uint32_t sTiles = sTmem + 16;                        // [kTileRing] published work tiles (-1: no more)
+  const uint32_t sTiles = (sTmem + 16 + 15u) & ~15u;         // [kTileRing] published work tiles, 64 bytes each
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));     // generic pointer to `base`
   auto bar = [&](int i) { return sBar + 8u * i; };
-  // the cnt-th work tile of this CTA (every reader calls this once per tile, in order); -1 = the CTA is done
-  auto next_tile = [&](int& cnt) {
+  // The cnt-th work tile of this CTA, everything a role needs to know about it, computed ONCE by the scheduler
+  // warp: every reader takes the entries in order (acquire), reads what it needs when it needs it (the copy costs a
+  // few shared-memory loads - no global loads, no divisions) and lets go of the entry when it is DONE with the tile.
+  auto acquire_tile = [&](int& cnt) {
     const int e = cnt % kTileRing;
     mbar_wait(bar(kBarTFull + e), (cnt / kTileRing) & 1);
-    int L;
-    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(L) : "r"(sTiles + 4u * e) : "memory");
-    mbar_arrive(bar(kBarTEmpty + e));
     ++cnt;
-    return L;
+    return e;
   };
+  auto read_tile = [&](int e, WorkTile& T) {
+    int4* d = reinterpret_cast<int4*>(&T);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(d[i].x), "=r"(d[i].y), "=r"(d[i].z), "=r"(d[i].w)
+                   : "r"(sTiles + 64u * e + 16u * i) : "memory");
+  };
+  auto release_tile = [&](int e) { mbar_arrive(bar(kBarTEmpty + e)); };
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool trace_cta = p.trace != nullptr && cta == 0;     // stamps of this CTA's FIRST work tile only
@@ -264,29 +277,28 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
 
     // The warpgroup's own walk over the CTA's work tiles: `item0` = ring items (K / V tiles) the CTA streamed
     // before the current work tile - every valid tile counts, also those this warpgroup has no rows in.
-    // Only the tile's index L and its ring position live across the KV loop; whatever else a phase needs is
-    // derived from L again (a few cached loads) - 232 registers hold a row of 128 scores and little else.
-    int t_cnt = 0, item0_next = 0;
-    int L_cur = -1, item0 = 0;
+    // Only the tile's ring entry lives across the KV loop; whatever a phase needs it reads from the entry again -
+    // 232 registers hold a row of 128 scores and little else.
+    int t_cnt = 0;
+    int e_cur = -1;
     // The CTA's next work tile: 1 = it has rows for this warpgroup, 0 = it has none (tile B of a short tail), -1 = no
     // more tiles.  Reads exactly one entry of the ring: the entry after a tile is published while that tile is still
     // being worked on, the one after THAT only once the tile is nearly done - a warpgroup in the middle of a tile
     // must never wait for it (the issuer would wait for the warpgroup, the producer for the issuer).
-    auto advance_one = [&](int& into_L, int& into_item0) -> int {
-      const int L = next_tile(t_cnt);
-      if (L < 0) return -1;
+    auto advance_one = [&](int& into_e) -> int {
+      const int e = acquire_tile(t_cnt);
       WorkTile c;
-      if (!work_tile(p, L, gx, R, c)) return 0;
-      const int at = item0_next;
-      item0_next += 2 * c.n;
-      if ((w == 0 ? c.ntok_a : c.ntok_b) == 0) return 0;
-      into_L = L;
-      into_item0 = at;
+      read_tile(e, c);
+      if (c.L < 0 || (w == 0 ? c.ntok_a : c.ntok_b) == 0) {
+        release_tile(e);
+        return c.L < 0 ? -1 : 0;
+      }
+      into_e = e;
       return 1;
     };
-    auto advance = [&](int& into_L, int& into_item0) -> bool {      // next work tile with rows for this warpgroup
+    auto advance = [&](int& into_e) -> bool {                       // next work tile with rows for this warpgroup
       for (;;) {
-        const int r = advance_one(into_L, into_item0);
+        const int r = advance_one(into_e);
         if (r != 0) return r > 0;
       }
     };
@@ -294,9 +306,9 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
     // Asynchronous copies (cp.async, 16 bytes each, rows past the tile's tokens zero-filled): nothing passes through
     // registers, so the copies of the NEXT work tile's Q are issued at the top of the current tile's last softmax
     // pass - every Q K^T of the tile has completed by then - and their global round trip is over when it ends.
-    auto stage_q_issue = [&](const int L) {
+    auto stage_q_issue = [&](const int e) {
       WorkTile c;
-      work_tile(p, L, gx, R, c);
+      read_tile(e, c);
       const int ntok_w = w == 0 ? c.ntok_a : c.ntok_b;
       const int tokw0 = c.tok0 + w * R;
       const __nv_bfloat16* qb = static_cast<const __nv_bfloat16*>(p.q);
@@ -325,15 +337,16 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
     };
 
     int s_cnt = 0, o_cnt = 0;                                // S tiles / work tiles this warpgroup has waited for so far
-    bool have = advance(L_cur, item0);
-    if (have) stage_q_commit(stage_q_issue(L_cur));
+    bool have = advance(e_cur);
+    if (have) stage_q_commit(stage_q_issue(e_cur));
     bool first_tile = true;
     while (have) {
-      int n_w, n, posw0, qpos, slot;
+      int n_w, n, posw0, qpos, slot, item0;
       bool valid;
       {
         WorkTile T;
-        work_tile(p, L_cur, gx, R, T);
+        read_tile(e_cur, T);
+        item0 = T.item0;
         const int ntok_w = w == 0 ? T.ntok_a : T.ntok_b;
         n_w = w == 0 ? T.n_a : T.n_b;
         n = T.n;
@@ -351,7 +364,7 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
       }
       const bool trace_on = trace_cta && first_tile && (tid & 127) == 0;
       float m_used = -INFINITY, l = 0.f;
-      int L_n = -1, item0_n = 0, slot_n = 0, next_state = 0;
+      int e_n = -1, slot_n = 0, next_state = 0;
 
       for (int t = 0; t < n_w; ++t) {
         uint32_t v[kTileN];
@@ -362,8 +375,8 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
         PA_TRACE(5 * w + 0, t);
         tc_fence_after();
         if (t == n_w - 1) {                                  // the tile's last S: its Q tile is not read any more
-          next_state = advance_one(L_n, item0_n);
-          if (next_state > 0) slot_n = stage_q_issue(L_n);
+          next_state = advance_one(e_n);
+          if (next_state > 0) slot_n = stage_q_issue(e_n);
         }
         // the scores arrive in two halves: the row maximum of keys [0, 64) is taken while keys [64, 128)
         // are still on their way from TMEM (tiles that need the causal / ragged mask wait for both first)
@@ -423,7 +436,7 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
         // ---- the work tile's last KV tile: V rows that were not loaded or lie beyond the context must be finite ----
         if (t == n - 1) {
           WorkTile T;
-          work_tile(p, L_cur, gx, R, T);
+          read_tile(e_cur, T);
           const int zero_from = min(T.nblk_need * kBS, T.ctx) - kbase;
           if (zero_from < kTileN) {
             const int item = item0 + 2 * t + 1;
@@ -485,7 +498,7 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
       __nv_bfloat16* ob;
       {
         WorkTile T;
-        work_tile(p, L_cur, gx, R, T);
+        read_tile(e_cur, T);
         ob = static_cast<__nv_bfloat16*>(p.out) + (int64_t)(T.q_start + T.tok0 + w * R + ti) * p.o_stride_t +
              (int64_t)(T.h * g + j) * p.o_stride_h;
       }
@@ -510,13 +523,13 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
       // O is read: the next tile's first P V may overwrite it.  That MMA is issued behind this warpgroup's
       // next P-ready arrival, which every thread makes after this point.
       tc_fence_before();
+      release_tile(e_cur);                                   // done with the tile: its entry may be overwritten
       bool have_n = next_state > 0;
       if (next_state == 0) {                                 // the next tile had no rows for this warpgroup: now it may wait
-        have_n = advance(L_n, item0_n);
-        if (have_n) stage_q_commit(stage_q_issue(L_n));
+        have_n = advance(e_n);
+        if (have_n) stage_q_commit(stage_q_issue(e_n));
       }
-      L_cur = L_n;
-      item0 = item0_n;
+      e_cur = e_n;
       have = have_n;
       first_tile = false;
     }
@@ -526,14 +539,15 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
   if (warp == 8) {
     // =============================== TMA producer ===============================
     const int b = lane / HALVES, hf = lane % HALVES;
-    int item0 = 0, t_cnt = 0;
+    int t_cnt = 0;
     for (;;) {
-      int L = 0;
-      if (lane == 0) L = next_tile(t_cnt);
-      L = __shfl_sync(FULL, L, 0);
-      if (L < 0) break;
+      const int e = acquire_tile(t_cnt);                     // every lane waits: the entry is read by all of them
       WorkTile T;
-      if (!work_tile(p, L, gx, R, T)) continue;
+      read_tile(e, T);
+      __syncwarp();
+      if (lane == 0) release_tile(e);                        // the copy is all this role needs
+      if (T.L < 0) break;
+      const int item0 = T.item0;
       const int32_t* bt = p.block_tables + (int64_t)T.s * p.bt_stride;
       for (int t = 0; t < T.n; ++t) {
         if (t == max(T.n - 1 - kDrawAhead, 0) && lane == 0) mbar_arrive(bar(kBarTReq));
@@ -553,7 +567,6 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
           if (mine) tma_load_half(sRing + (uint32_t)slot * kItem + in_item, kv ? &tm_v : &tm_k, bar(kBarKvFull + slot), hf, c3, c4);
         }
       }
-      item0 += 2 * T.n;
     }
   } else if (warp == 9) {
     // =============================== MMA issuer ===============================
@@ -601,14 +614,19 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
       };
       int t_cnt = 0;
       for (;;) {
-        const int L = next_tile(t_cnt);
-        if (L < 0) break;
-        WorkTile T;
-        if (!work_tile(p, L, gx, R, T)) continue;
-        const int n = T.n, n_a = T.n_a, n_b = T.n_b;
+        int n, n_a, n_b, ntok_b;
+        {
+          const int e = acquire_tile(t_cnt);
+          WorkTile T;
+          read_tile(e, T);
+          release_tile(e);
+          if (T.L < 0) break;
+          n = T.n; n_a = T.n_a; n_b = T.n_b; ntok_b = T.ntok_b;
+          item0 = T.item0;
+        }
         mbar_wait(bar(kBarQReady), ph & 1u);
         ph ^= 1u;
-        if (T.ntok_b > 0) {
+        if (ntok_b > 0) {
           mbar_wait(bar(kBarQReady + 1), (ph >> 1) & 1u);
           ph ^= 2u;
         }
@@ -631,7 +649,6 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
           free_item(item0 + 2 * t + 1);
           if (t + 1 < n) free_item(item0 + 2 * t + 2);
         }
-        item0 += 2 * n;
         tr = false;
       }
       tc_fence_before();
@@ -641,10 +658,18 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
     // =============================== work-tile scheduler ===============================
     int* const tk = g_tickets + 2 * ticket_slot;
     int pub = 0;
-    auto publish = [&](int L) {                              // lane 0
+    int items = 0;                                           // K / V ring items of the tiles published so far
+    auto publish = [&](WorkTile& T, int L) {                 // lane 0
       const int e = pub % kTileRing;
       mbar_wait(bar(kBarTEmpty + e), ((pub / kTileRing) & 1) ^ 1);
-      asm volatile("st.shared.b32 [%0], %1;" ::"r"(sTiles + 4u * e), "r"(L) : "memory");
+      T.L = L;
+      T.item0 = items;
+      T.pad = 0;
+      const int4* src = reinterpret_cast<const int4*>(&T);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sTiles + 64u * e + 16u * i), "r"(src[i].x), "r"(src[i].y),
+                     "r"(src[i].z), "r"(src[i].w) : "memory");
       mbar_arrive(bar(kBarTFull + e));
       ++pub;
     };
@@ -660,7 +685,8 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
       if (L >= total_tiles) break;
       WorkTile T;
       if (work_tile(p, L, gx, R, T)) {
-        if (lane == 0) publish(L);
+        if (lane == 0) publish(T, L);
+        items += 2 * T.n;
         ++drawn;
         continue;
       }
@@ -683,7 +709,9 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
       if (lane == 0) atomicMax(tk, found * hkv);
     }
     if (lane == 0) {
-      publish(-1);
+      WorkTile T;
+      memset(&T, 0, sizeof(T));
+      publish(T, -1);
       // every CTA draws exactly one ticket past the end, after its last touch of the slot: the last to do so clears it
       if (atomicAdd(tk + 1, 1) == (int)gridDim.x - 1) {
         tk[0] = 0;
@@ -703,7 +731,7 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
 
 template <int HD>
 constexpr size_t smem_bytes() {
-  return 1024 + (size_t)(HD / 64) * kSlab * (2 + kRing) + kNumBars * 8 + 16 + kTileRing * 4;
+  return 1024 + (size_t)(HD / 64) * kSlab * (2 + kRing) + kNumBars * 8 + 16 + 16 + kTileRing * 64;
 }
 
 int sm_count_cached() {
