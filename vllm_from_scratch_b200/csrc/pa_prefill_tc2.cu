@@ -596,13 +596,15 @@ pa_prefill_tc2_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_con
       };
       auto pv = [&](int w, int t, bool last) {               // O_w += P_w V(t)      (P in TMEM, V in shared memory)
         // the first 64 keys' P V runs while the warpgroup still exponentiates the other 64
+        // everything that can be computed before P is ready is: the issuer is ONE thread, and what it executes
+        // between a barrier flipping and the MMA going out is added to every tile
         const uint32_t par = (ph >> (2 + w)) & 1u;
         ph ^= 4u << w;
+        const uint64_t db = kDescV | (uint64_t)(((sRing + (uint32_t)((item0 + 2 * t + 1) % kRing) * kItem) & 0x3FFFFu) >> 4);
+        const uint32_t d = tmem + kTmemO + (uint32_t)w * 128u, a = tmem + (uint32_t)w * 128u;
         mbar_wait(bar(kBarPReady + 2 * w), par);
         if (tr && t < kTraceTiles) p.trace[t * kTraceSlots + 10 + 2 * w] = clock64();
         tc_fence_after();
-        const uint64_t db = kDescV | (uint64_t)(((sRing + (uint32_t)((item0 + 2 * t + 1) % kRing) * kItem) & 0x3FFFFu) >> 4);
-        const uint32_t d = tmem + kTmemO + (uint32_t)w * 128u, a = tmem + (uint32_t)w * 128u;
         umma_bf16_ts(d, a, db, idesc_o, t > 0 ? 1u : 0u);
 #pragma unroll
         for (int ks = 1; ks < kTileN / 32; ++ks) umma_bf16_ts(d, a + (uint32_t)ks * 8u, db + (uint64_t)(ks * (16 * 128 >> 4)), idesc_o, 1u);
