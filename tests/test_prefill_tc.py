@@ -169,3 +169,44 @@ def test_prefill_tc_long_context_chunk(P):
     got = P.paged_attention_prefill_chunk(q[total - n:].to(DEV), kv.to(DEV), bt_dev, total - n)
     ref = O.chunked_prefill_hbsd(q[total - n:], kv, bt, total - n, bs, compute_dtype=torch.float64)
     assert (got.double().cpu() - ref).abs().max().item() <= TOL
+
+
+def test_prefill_tc_persistent_scheduler_sparse_batch(P):
+    """More work tiles than SMs, most of them empty: one long prompt next to many one-token rows and masked rows
+    (q_len 0).  The persistent kernel's scheduler warp has to skip the empty tiles of the launch's ticket list,
+    every CTA walks several tiles (barrier phases carried across tiles), and tiles without a second query tile
+    (a warpgroup with no rows) sit between tiles that have one."""
+    g = torch.Generator().manual_seed(21)
+    hq, hkv, d, bs = 32, 8, 128, 16
+    specs = [(1400, 1400)] + [(40 + 7 * i, 1) for i in range(40)] + [(64, 0)] * 6 + [(333, 97), (200, 33), (96, 96)]
+    nb = sum((c + bs - 1) // bs for c, _ in specs) + 8
+    q, kv, bts, cu, ctx, ref = _varlen_batch(g, specs, hq, hkv, d, bs, nb)
+    args = (q.to(DEV), kv.to(DEV), bts.to(DEV), cu.to(DEV), ctx.to(DEV), max(ql for _, ql in specs))
+    got = P.paged_attention_prefill_varlen(*args)
+    assert (got.double().cpu() - ref).abs().max().item() <= TOL
+    # the launch leaves its ticket slot clean: the same call again (and again) gives the same bits
+    for _ in range(3):
+        again = P.paged_attention_prefill_varlen(*args)
+        assert torch.equal(again, got)
+
+
+def test_prefill_tc_concurrent_launches_on_two_streams(P):
+    """Two launches in flight at once draw their work tiles from different ticket slots."""
+    g = torch.Generator().manual_seed(22)
+    hq, hkv, d, bs = 32, 8, 128, 16
+    batches = []
+    for specs in ([(900, 900), (300, 1), (650, 130)], [(1100, 700), (80, 80), (500, 1), (64, 0)]):
+        nb = sum((c + bs - 1) // bs for c, _ in specs) + 4
+        q, kv, bts, cu, ctx, ref = _varlen_batch(g, specs, hq, hkv, d, bs, nb)
+        batches.append(((q.to(DEV), kv.to(DEV), bts.to(DEV), cu.to(DEV), ctx.to(DEV), max(ql for _, ql in specs)), ref))
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    outs = [[], []]
+    for _ in range(4):
+        for i, (args, _) in enumerate(batches):
+            with torch.cuda.stream(streams[i]):
+                outs[i].append(P.paged_attention_prefill_varlen(*args))
+    torch.cuda.synchronize()
+    for i, (_, ref) in enumerate(batches):
+        for got in outs[i]:
+            assert (got.double().cpu() - ref).abs().max().item() <= TOL

@@ -23,6 +23,11 @@
 //   * softmax per thread = one row of 128 scores: one tcgen05.ld pass, FMNMX3 row max, FFMA2 /
 //     ex2 / FADD2 (packed fp32x2), bf16 pack.  The O accumulator is rescaled only when a row's
 //     maximum grew by more than 2^8 over the maximum in use (exact: l and O share that reference).
+//   * persistent (round 2): one CTA per SM; warp 10 draws work tiles (2 * R tokens of one (sequence, KV head),
+//     longest first) from a per-launch ticket, as late as it can, and publishes each tile's descriptor through
+//     shared memory to the other roles.  Barriers, TMEM and the register split are set up once per CTA, the
+//     K / V ring never drains across tiles, and a warpgroup's next Q tile is staged with cp.async under its
+//     last softmax pass.  Per work tile the fixed cost went from 6.2 us + 3.5 us between CTAs to ~4.7 us + 0.6.
 // TMEM (512 columns): S_A / P_A [0,128) | S_B / P_B [128,256) | O_A [256,384) | O_B [384,512).
 // Shared memory (D = 128): Q_A, Q_B 32 KiB each | ring 5 x 32 KiB = 224 KiB.
 #include <atomic>
