@@ -322,9 +322,14 @@ int pa_swap_blocks_staged(void* dev_base, int64_t dev_plane_stride_bytes, int64_
  * q / out [num_tokens, num_q_heads, D].  One sequence per call.
  * Two implementations behind this entry:
  *  - tensor-core path (bf16, block_size 16, head_dim 64 / 128, g a power of
- *    two <= 16, 16-byte aligned strides): pa_prefill_tc_kernel, tcgen05.mma
+ *    two <= 16, 16-byte aligned strides): pa_prefill_tc2_kernel, tcgen05.mma
  *    with TMEM accumulators, K / V tiles gathered by TMA through the block
- *    table (csrc/pa_prefill_tc.cu);
+ *    table (csrc/pa_prefill_tc2.cu).  Persistent, one CTA per SM; the CTAs
+ *    draw their work tiles from a per-launch ticket kept in a 1024-slot
+ *    device array inside the library (slot = launch number mod 1024, put back
+ *    to zero by the launch's last CTA): no workspace, any number of launches
+ *    in flight on any streams - two launches share a slot only if 1024
+ *    launches apart AND running at the same time;
  *  - everything else (fp32 caches, the engine's toy head sizes): every query
  *    token is a decode "sequence" of length start_pos + i + 1 over the shared
  *    block table (same kernels and numerics as pa_decode).                   */

@@ -1,6 +1,9 @@
-"""Experiment (not part of the product): where a prefill CTA's time goes.  Per-CTA globaltimer stamps
-of pa_prefill_tc2_kernel (pa_prefill_debug_times) on the bench_prefill shapes: prologue, Q staging,
-time to the first S tile, steady state per KV tile, epilogue, and the gap between two CTAs on one SM."""
+"""Experiment (not part of the product): where a prefill work tile's time goes.  Per-work-tile globaltimer
+stamps of pa_prefill_tc2_kernel (pa_prefill_debug_times) on the bench_prefill shapes.  The kernel is persistent
+(one CTA per SM walks the work tiles), so "CTA" below reads "work tile": [1] = warpgroup A starts on the tile (its
+previous tile's output is stored), [3] = its Q tile staged (BEFORE [1] for every tile but a CTA's first: it is
+staged under the previous tile's last softmax pass), [4] first S ready, [5] O complete, [6] outputs stored; the
+same-SM gap is the time between two consecutive tiles of one CTA."""
 import os
 import sys
 
