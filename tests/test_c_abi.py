@@ -72,6 +72,27 @@ def test_status_strings_and_argument_validation_without_a_gpu(lib):
     assert lib.pa_copy_blocks(None, 0, 0, 0, 0, None, 0, None) == 0
 
 
+def test_static_scratch_decode_validates_before_it_touches_a_device(lib):
+    """pa_decode_static (no counterpart in the reference): the size check against PA_DECODE_STATIC_BYTES and the
+    argument checks come before any CUDA call, so they answer without a GPU."""
+    from vllm_from_scratch_b200._lib import PaKvCache, SIGNATURES
+    res, args = SIGNATURES["pa_decode_static"]
+    lib.pa_decode_static.restype, lib.pa_decode_static.argtypes = res, args
+    lib.pa_decode_workspace_bytes.restype = ctypes.c_size_t
+    lib.pa_decode_workspace_bytes.argtypes = [ctypes.c_int32] * 4
+    lib.pa_status_string.restype = ctypes.c_char_p
+    header = open(HEADER).read()
+    limit = int(re.search(r"#define PA_DECODE_STATIC_BYTES \((\d+)u << (\d+)\)", header).group(1)) << 20
+    assert limit == 96 << 20
+    c = PaKvCache(16, 16, 8 * 16 * 128, 16 * 128, 128, 64, 8, 16, 128, 0, 0)
+    assert lib.pa_decode_workspace_bytes(512, 64, 8, 128) > limit
+    rc = lib.pa_decode_static(16, 64 * 128, 128, 16, 64 * 128, 128, ctypes.byref(c), 16, 1, 16, 512, 64, None)
+    assert rc == -7 and b"static" in lib.pa_status_string(rc)
+    assert lib.pa_decode_static(16, 1, 1, 16, 1, 1, None, 16, 1, 16, 1, 4, None) == -1          # no cache descriptor
+    assert lib.pa_decode_static(None, 0, 0, None, 0, 0, ctypes.byref(c), None, 0, None, 0, 32, None) == 0   # empty batch
+    assert lib.pa_decode_static(16, 1, 1, 16, 1, 1, ctypes.byref(c), 16, 1, 16, -3, 32, None) == -1
+
+
 def test_torch_shim_loads_and_mirrors_the_error_contract():
     """The thin torch C++ extension (csrc/torch_shim.cpp) is built in-tree, reports the same ABI version and raises
     the host mirror's exception types without touching a device (CPU tensors: RuntimeError, no CPU fallback)."""
