@@ -121,8 +121,9 @@ int pa_decode(const void* q, int64_t q_stride_b, int64_t q_stride_h,
  *   (96 MiB holds e.g. batch <= 256 at 32 query / 8 KV heads of dim 128; the
  *   need grows with batch * num_q_heads * head_dim) - use pa_decode then.
  * Sharing: ALL calls on a device use the same array, which keeps the previous
- *   call's contents (the kernels leave their counters at zero and stamp partials
- *   with a per-launch epoch, so nothing needs clearing between calls).  Calls
+ *   call's contents (the two counters that must start at zero are cleared,
+ *   stream-ordered, before every launch; partials carry a per-launch epoch, so
+ *   stale ones never validate).  Calls
  *   that can overlap on the GPU - different streams without an ordering event -
  *   RACE on it: keep them on one stream, or use pa_decode with one workspace
  *   per stream.                                                               */

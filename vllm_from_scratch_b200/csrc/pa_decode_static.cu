@@ -7,12 +7,13 @@
 // loads this module holds the array until the process exits.  Nothing here (nor anything pa_decode reaches:
 // planning, tensor-map encoding, the kernel launches) calls cudaMalloc / cudaFree or an allocating library.
 //
-// State of the array between calls.  It is zero when the module is loaded (static storage).  The decode kernels
-// keep their own invariant on it, the one pa_decode documents for any workspace: the unit ticket and the
-// exited-CTA counter are back at zero when a call's last CTA exits, the launch epoch word advances by one, and
-// a partial word of an earlier call never validates because it carries that call's epoch.  So nothing has to be
-// cleared per call and nothing is; what a call leaves behind (epoch word, stale partials) is exactly what the
-// next one expects.  Every call on a device SHARES the array: two calls that can overlap on the GPU (different
+// State of the array between calls.  It is zero when the module is loaded (static storage) and keeps the last
+// call's contents afterwards.  What must start at zero is the unit ticket and the exited-CTA counter (the first
+// two words): the kernel puts them back itself when its last CTA exits, and this entry point clears them again,
+// stream-ordered, before every launch - eight bytes, so a call never depends on how the previous one ended.  What
+// must NOT be cleared is the launch epoch word behind them: it advances by one per launch, and a partial word an
+// earlier call left in the array never validates because it carries that call's epoch.  Every call on a device
+// SHARES the array: two calls that can overlap on the GPU (different
 // streams, or two host threads launching on unordered streams) race on the counters and on each other's
 // partials - order them on one stream or with events.  Concurrent use of pa_decode with a caller-owned
 // workspace is unaffected.
@@ -63,6 +64,8 @@ extern "C" int pa_decode_static(const void* q, int64_t q_stride_b, int64_t q_str
   void* ws = nullptr;
   const int rc = static_workspace(&ws);
   if (rc != PA_OK) return rc;
+  // the two counters that must be zero on entry (not the epoch word that follows them); a memset node, no allocation
+  if (cudaMemsetAsync(ws, 0, 8, static_cast<cudaStream_t>(stream)) != cudaSuccess) { cudaGetLastError(); return PA_ERR_CUDA; }
   return pa_decode(q, q_stride_b, q_stride_h, out, o_stride_b, o_stride_h, cache, block_tables, bt_stride, seq_lens,
                    batch, num_q_heads, ws, (size_t)PA_DECODE_STATIC_BYTES, stream);
 }
